@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""Benchmark of the ConceptAttention hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config NAME]
+
+metric  : concept-heatmap images/sec @1024^2 Flux-schnell (configs[1] of BASELINE.json:
+          4096 image tokens, 256 text tokens, 4 concepts, 4 denoising steps, bf16,
+          heatmaps from layers 15..18 of every step, both spaces).
+step    : one image = 4 x (19 double + 38 single blocks) + heatmap accumulation.
+value   : images/s with the step's inputs already resident in HBM (CUDA events).
+e2e     : images/s through ConceptAttentionFluxPipeline.generate_image with pinned
+          HOST inputs (latents, text/concept embeddings) copied H2D and the heatmaps
+          copied D2H inside the timed region.
+roofline: the fused joint-attention kernel (K2), timed live with CUDA events around
+          every launch of the timed region, against the measured bf16 peak.
+N > 1   : one process per GPU, each generates its own images (data parallel, no
+          collective on the path); NCCL is used for the barrier / max-over-ranks only.
+--impl reference : the CPU oracle (port of the reference's PyTorch path; the reference
+          itself is Python and does not travel) on all host cores, bounded sample.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "concept-heatmap images/sec @1024^2 Flux-schnell"
+WORKLOADS = {
+    # name: model, side, concepts, steps, layers
+    "schnell-1024": dict(model="flux-schnell", side=1024, C=4, nsteps=4, layers=list(range(15, 19))),
+    "tiny-256": dict(model="tiny", side=256, C=4, nsteps=2, layers=[1, 2]),     # debug only
+}
+D_HEAD = 128
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(tflops=p["bf16_tflops_sustained"], tflops_burst=p["bf16_tflops"],
+                    hbm=p["hbm_gbs"], source="measured (MEASURED_PEAKS.json, sustained)")
+    return dict(tflops=1400.0, tflops_burst=1590.0, hbm=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def attention_flops(P, T, C, H, double):
+    """ALGORITHMIC FLOPs of one K2 launch per batch element."""
+    f = 4 * D_HEAD * H * (T + P) ** 2
+    return f + (4 * D_HEAD * H * C * (C + P) if double else 0)
+
+
+def run_ours(args, rank, world, local_rank):
+    from conceptattention_b200 import ConceptAttentionFluxPipeline, ops, sampling
+    from conceptattention_b200.dit import HeatmapAccumulator
+    wl = WORKLOADS[args.config]
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    side, C, nsteps, layers = wl["side"], wl["C"], wl["nsteps"], wl["layers"]
+    concepts = ["dragon", "rock", "sky", "sun", "tree", "grass", "cloud", "river"][:C]
+    prompt = "A dragon standing on a rock"
+    # text encoders on the HOST (pinned) so the e2e arm pays the H2D copy of their outputs
+    pipe = ConceptAttentionFluxPipeline(model_name=wl["model"], device=dev, seed=rank)
+    gen = pipe.flux_generator
+    pm = gen.params
+    host_t5 = sampling.SyntheticEmbedder(pm.context_in_dim, gen.t5.max_length, "cpu")
+    host_clip = sampling.SyntheticEmbedder(pm.vec_in_dim, None, "cpu")
+    for e, texts in ((host_t5, [prompt] + concepts), (host_clip, [prompt, " ".join(concepts)])):
+        for t in texts:
+            e(t)
+        e._cache = {k: v.pin_memory() for k, v in e._cache.items()}
+    host_lat = [torch.randn(1, 16, side // 8, side // 8, generator=torch.Generator().manual_seed(1000 * rank + i))
+                .to(torch.bfloat16).pin_memory() for i in range(args.steps + args.warmup)]
+    dev_lat = [l.to(dev) for l in host_lat]
+    P, T, H = (side // 16) ** 2, gen.t5.max_length, pm.num_heads
+    sched = sampling.get_schedule(nsteps, P, shift=(not gen.is_schnell))
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    # ---- arm 1: inputs resident in HBM ------------------------------------------------
+    inps = [gen.prepare_inputs(prompt, concepts, l) for l in dev_lat]
+
+    def device_step(i):
+        acc = HeatmapAccumulator(1, C, P, dev, layers, list(range(nsteps)), True, "sparsemax")
+        gen.denoise(inps[i], sched, 0.0, acc)
+        return acc.finalize()
+
+    for i in range(args.warmup):
+        device_step(i)
+    barrier()
+    ops.LAUNCHES = 0
+    ops.ATTN_EVENTS = []
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        device_step(args.warmup + i)
+    e1.record()
+    barrier()
+    ms_dev = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    launches = ops.LAUNCHES
+    attn_ms = sum(ev[0].elapsed_time(ev[1]) for ev, *_ in ops.ATTN_EVENTS)
+    n_attn = len(ops.ATTN_EVENTS)
+    attn_flops = sum(B * attention_flops(Pq, Tq, Cq, H, Cq > 0) for _, B, Pq, Tq, Cq in ops.ATTN_EVENTS)
+    ops.ATTN_EVENTS = None
+
+    # ---- arm 2: end to end through the public API with host buffers ---------------------
+    gen.t5, gen.clip = host_t5, host_clip
+
+    def e2e_step(i):
+        return pipe.generate_image(prompt, concepts, width=side, height=side, layer_indices=layers,
+                                   return_pil_heatmaps=False, num_inference_steps=nsteps,
+                                   latents=host_lat[i], decode_image=False)
+    for i in range(args.warmup):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        out = e2e_step(args.warmup + i)
+    e1.record()
+    barrier()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)
+    h2d = (host_lat[0].numel() * 2 + T * pm.context_in_dim * 2 + pm.vec_in_dim * 2 * 2
+           + C * pm.context_in_dim * 2)
+    d2h = 2 * C * P * 4
+
+    if world > 1:
+        t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ms_dev, ms_e2e = t.tolist()
+    pk = peaks()
+    ach = attn_flops / (attn_ms * 1e-3) / 1e12 if attn_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "k2_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    line = {
+        "metric": METRIC, "value": world * args.steps / (ms_dev * 1e-3), "unit": "images/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random-init weights, randn latents/embeddings)",
+        "config": {"workload": f"{args.config}: {wl['model']} {side}x{side}, P={P} T={T} C={C}, "
+                               f"{nsteps} denoise steps x (19 double + 38 single blocks), heatmaps from "
+                               f"layers {layers[0]}..{layers[-1]} both spaces",
+                   "images_per_step_per_gpu": 1, "parallelism": f"dp{world} (one image stream per GPU, no collective)",
+                   "cache": "inputs larger than L2: 23.8 GB of bf16 weights stream through every step"},
+        "e2e": {"value": world * args.steps / (ms_e2e * 1e-3), "unit": "images/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": launches,
+        "clocks": clk,
+        "roofline": {"kernel": "ca_joint_attention (K2, tcgen05 one-way joint attention)",
+                     "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
+                     "frac": ach / pk["tflops"], "peak_source": pk["source"], "traffic": traffic,
+                     "launches_timed": n_attn, "avg_launch_ms": attn_ms / max(n_attn, 1),
+                     "share_of_step": attn_ms / ms_dev},
+    }
+    return line, out
+
+
+def run_reference(args):
+    """CPU arm: the oracle (fp32 port of the reference's PyTorch path, executing the same
+    op sequence incl. the full (C+P)^2 second attention and the stack-then-einsum heatmap
+    step) on all host cores.  One step = a bounded SAMPLE of one image of the workload:
+    1 double block + 1 single block + the heatmap computation of one (timestep, 4 layers)
+    slice at full dimensions, extrapolated linearly:
+        t_image = nsteps * (19 t_double + 38 t_single) + nsteps * t_heat
+    (the reference's model-independent glue — embeddings, final layer — is < 0.1 %)."""
+    import oracle
+    from conceptattention_b200.weights import CONFIGS, FluxParams, init_state_dict
+    wl = WORKLOADS[args.config]
+    pm = CONFIGS[wl["model"]]
+    cores = os.cpu_count()
+    torch.set_num_threads(cores)
+    torch.set_grad_enabled(False)
+    side, C, nsteps, layers = wl["side"], wl["C"], wl["nsteps"], wl["layers"]
+    D, H = pm.hidden_size, pm.num_heads
+    P, T = (side // 16) ** 2, {"flux-schnell": 256, "flux-dev": 512}.get(wl["model"], 128)
+    one = FluxParams(**{**pm.asdict(), "depth": 1, "depth_single_blocks": 1})
+    sd = init_state_dict(one, seed=0)
+    g = torch.Generator().manual_seed(0)
+    img, txt, con = (torch.randn(1, n, D, generator=g) for n in (P, T, C))
+    vec, cvec = torch.randn(1, D, generator=g), torch.randn(1, D, generator=g)
+    ids = oracle.image_ids(1, side // 16, side // 16)
+    pe = oracle.rope_table(torch.cat((torch.zeros(1, T, 3), ids), 1), pm.axes_dim, pm.theta)
+    pe_c = oracle.rope_table(torch.cat((torch.zeros(1, C, 3), ids), 1), pm.axes_dim, pm.theta)
+    nl = len(layers)
+
+    def sample():
+        t0 = time.perf_counter()
+        i2, t2, c2, vecs = oracle.double_block(sd, "double_blocks.0", H, img, txt, vec, pe, con, cvec, pe_c)
+        t1 = time.perf_counter()
+        oracle.single_block(sd, "single_blocks.0", H, torch.cat((t2, i2), 1), vec, pe)
+        t2_ = time.perf_counter()
+        for a, b in (("output_space_image_vectors", "output_space_concept_vectors"),
+                     ("cross_attention_image_vectors", "cross_attention_concept_vectors")):
+            iv = vecs[a][None, None].expand(1, nl, *vecs[a].shape)
+            cv = vecs[b][None, None].expand(1, nl, *vecs[b].shape)
+            oracle.heatmaps_from_vectors(iv, cv, list(range(nl)), [0])
+        t3 = time.perf_counter()
+        return nsteps * (pm.depth * (t1 - t0) + pm.depth_single_blocks * (t2_ - t1)) + nsteps * (t3 - t2_)
+
+    w0 = time.perf_counter()
+    for _ in range(max(args.warmup, 1)):
+        sample()
+    per_sample = (time.perf_counter() - w0) / max(args.warmup, 1)
+    steps = max(1, min(args.steps, int(150.0 / max(per_sample, 1e-3))))
+    est = [sample() for _ in range(steps)]
+    t_img = statistics.mean(est)
+    val = 1.0 / t_img
+    desc = (f"per step: 1 double block + 1 single block + heatmaps of 1 timestep x {nl} layers x 2 spaces at "
+            f"full size (P={P},T={T},C={C},D={D}) fp32, extrapolated to {nsteps} steps x (19+38) blocks")
+    return {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": max(args.warmup, 1), "ms_per_step": t_img * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic (random-init weights, randn inputs)",
+        "config": {"workload": f"{args.config}: {wl['model']} {side}x{side}, P={P} T={T} C={C}, {nsteps} denoise steps",
+                   "note": "CPU host cores; rank 0 only; bounded sample extrapolated"},
+        "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="schnell-1024", choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps(run_reference(args)), flush=True)
+        return
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    args.warmup = max(args.warmup, 3)
+    line, _ = run_ours(args, rank, world, local_rank)
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            torch.cuda.empty_cache()
+            ref = run_reference(argparse.Namespace(config=args.config, steps=2, warmup=1, gpus=1))
+            line["cpu_baseline"] = ref["cpu_baseline"]
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,79 @@
+"""ctypes binding of libconceptattention_b200.so (include/conceptattention_b200.h).
+
+The library is the product: if it cannot be loaded this module raises — there is
+no eager/PyTorch fallback anywhere in the package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch  # noqa: F401  (loads libcudart.so.12 that the library links against)
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libconceptattention_b200.so")
+
+CA_OK = 0
+NORM = {"softmax": 0, "sparsemax": 1, "entmax15": 2, "none": 3}
+ATTN_BOTH, ATTN_CROSS_ONLY, ATTN_SELF_ONLY, ATTN_NEITHER = 0, 1, 2, 3
+
+_p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
+
+# name -> argtypes; restype is int (ca_status) unless listed in _RESTYPES
+SIGNATURES = {
+    "ca_version": [],
+    "ca_status_string": [_i],
+    "ca_last_cuda_error": [],
+    "ca_device_check": [_i],
+    "ca_ln_modulate": [_p, _p, _i, _i, _i, _p, _p, _i, _i64, _i, _i, _p],
+    "ca_gate_residual_ln_modulate": [_p, _p, _i64, _p, _i, _i, _i, _p, _p, _i, _i64, _i, _i, _i, _p],
+    "ca_qkv_prep": [_p, _i64, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p],
+    "ca_joint_attention": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p],
+    "ca_heatmap_accumulate": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p],
+    "ca_heatmap_logits": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _p, _p],
+    "ca_norm_accumulate": [_p, _i, _i, _i, _i, _i, _p, _p],
+    "ca_concept_linear_normalize": [_p, _p, _i, _i64, _p],
+    "ca_finalize_heatmaps": [_p, _p, _i64, _f, _i, _p],
+    "ca_gaussian_blur3": [_p, _p, _i, _i, _i, _p],
+    "ca_argmax_mask": [_p, _p, _i, _i, _i, _i, _p],
+    "ca_binary_masks": [_p, _p, _i, _i, _p],
+    "ca_heatmaps_from_vectors_host": [_p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _i, _i, _p],
+}
+_RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p}
+
+_lib = None
+
+
+class ConceptAttentionLibraryError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def load():
+    """dlopen the library and bind every declared symbol (raises if absent)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise ConceptAttentionLibraryError(
+            f"{_LIB_PATH} not found: run `python -m conceptattention_b200.build` "
+            "(there is no CPU / PyTorch fallback)")
+    lib = C.CDLL(_LIB_PATH)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the .so is stale
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPES.get(name, C.c_int)
+    lib.ca_debug_set_attention_impl.argtypes = [_i]
+    lib.ca_debug_set_attention_impl.restype = None
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str):
+    if status != CA_OK:
+        lib = load()
+        msg = lib.ca_status_string(status).decode()
+        extra = f" (cuda error {lib.ca_last_cuda_error()})" if status == -5 else ""
+        raise ConceptAttentionLibraryError(f"{what}: {msg}{extra}")

@@ -1,0 +1,354 @@
+// K2: one-way joint MM-DiT attention on tcgen05 / TMEM / TMA (sm_100a).
+//
+// Replaces concept_attention/modified_double_stream_block.py:106-176 — two
+// F.scaled_dot_product_attention calls over cat(txt,img) and cat(concept,img) —
+// with ONE launch over a packed sequence [img | txt | concept] per (batch, head):
+//   query rows [0, P+T)       see keys [0, P+T)
+//   query rows [P+T, P+T+C)   see keys [0, P) U [P+T, P+T+C)   (ablation modes trim this)
+// so the image stream is bit-identical to attention without concepts and the
+// (C+P)^2 - C(C+P) image rows of the reference's second call are never computed.
+//
+// Tiling: 128 query rows x 128 keys x d=128, bf16 operands, fp32 accumulation.
+//   S = Q K^T : tcgen05.mma kind::f16, A = Q tile (smem, K-major SW128),
+//               B = K tile (smem, K-major SW128), D = S in TMEM (128 lanes x 128 cols)
+//   O += P V  : A = P (bf16), B = V tile (smem, MN-major SW128), D = O in TMEM
+// Tiles arrive by TMA (cp.async.bulk.tensor, 128B swizzle, zero OOB fill) and are
+// tracked with mbarriers; MMA completion is signalled with tcgen05.commit.
+#include "ca_common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace ca {
+
+using namespace ptx;
+
+constexpr int kD = CA_HEAD_DIM;        // 128
+constexpr int kBM = 128;               // query rows per tile
+constexpr int kBN = 128;               // keys per tile
+constexpr int kTileBytes = kBM * kD * 2;          // 32 KB: one 128x128 bf16 tile
+constexpr int kHalfBytes = kTileBytes / 2;        // 16 KB: one 128x64 swizzle block
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kRescaleThreshold = 8.0f;         // lazy rescale: keep the stale max while
+                                                  // exp2 arguments stay <= 8 (P <= 256)
+
+struct AttnParams {
+  int B, H, P, T, C, mode;
+  int n_main_tiles;                    // ceil((P+T)/128)
+  __nv_bfloat16* out_img;              // [B,P,H*128]
+  __nv_bfloat16* out_txtc;             // [B,T+C,H*128]
+  float scale_log2;                    // log2(e)/sqrt(128)
+};
+
+// Key ranges visible to a query tile: up to two half-open row segments.
+struct KeySegs { int s0, e0, s1, e1; };
+
+__device__ __forceinline__ KeySegs key_segments(const AttnParams& p, bool concept_tile) {
+  const int PT = p.P + p.T;
+  if (!concept_tile) return {0, PT, 0, 0};
+  if (p.mode == CA_ATTN_CROSS_ONLY) return {0, p.P, 0, 0};
+  if (p.mode == CA_ATTN_SELF_ONLY) return {PT, PT + p.C, 0, 0};
+  return {0, p.P, PT, PT + p.C};
+}
+
+__device__ __forceinline__ int tiles_of(int s, int e) { return (e - s + kBN - 1) / kBN; }
+
+// key tile j of the segments -> first row and number of valid rows
+__device__ __forceinline__ void key_tile(const KeySegs& ks, int n0, int j, int& row0, int& valid) {
+  if (j < n0) { row0 = ks.s0 + j * kBN; valid = min(kBN, ks.e0 - row0); }
+  else        { row0 = ks.s1 + (j - n0) * kBN; valid = min(kBN, ks.e1 - row0); }
+}
+
+// Write 8 consecutive bf16 (one 16-byte chunk) of row r, columns [c8*8, c8*8+8) into a
+// K-major SWIZZLE_128B operand tile made of two 128x64 blocks.
+__device__ __forceinline__ void st_swizzled_chunk(uint8_t* tile, int r, int c8, uint4 val) {
+  const int blk = c8 >> 3, cc = c8 & 7;
+  *reinterpret_cast<uint4*>(tile + blk * kHalfBytes + r * 128 + ((cc ^ (r & 7)) << 4)) = val;
+}
+
+__device__ __forceinline__ void store_out_row(const AttnParams& p, int b, int h, int row,
+                                              const float* o, float inv_l, int c0, int ncols) {
+  // row is an index into the packed sequence; img rows -> out_img, the rest -> out_txtc
+  const int HD = p.H * kD;
+  __nv_bfloat16* dst = row < p.P
+      ? p.out_img + ((int64_t)b * p.P + row) * HD + h * kD
+      : p.out_txtc + ((int64_t)b * (p.T + p.C) + (row - p.P)) * HD + h * kD;
+#pragma unroll
+  for (int c = 0; c < ncols; c += 8) {
+    float t[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t[j] = o[c + j] * inv_l;
+    *reinterpret_cast<uint4*>(dst + c0 + c) = pack8(t);
+  }
+}
+
+// =============================================================================
+// v0: one 128-row query tile per CTA, 128 threads, synchronous softmax.  Thread 0
+// issues TMA and MMA; every thread owns one query row (TMEM lane == thread).
+// Kept as the simple, obviously-correct implementation the pipelined kernel is
+// validated against.
+// =============================================================================
+struct SmemV0 {
+  uint8_t q[kTileBytes];
+  uint8_t k[2][kTileBytes];
+  uint8_t v[2][kTileBytes];
+  uint8_t p[kTileBytes];
+  uint64_t bar_q, bar_k[2], bar_v[2], bar_s, bar_o;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(128, 1)
+attn_v0_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+               const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV0& sm = *reinterpret_cast<SmemV0*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
+  const bool concept_tile = (int)blockIdx.x >= p.n_main_tiles;
+  const int PT = p.P + p.T;
+  const int q_row0 = concept_tile ? PT : blockIdx.x * kBM;
+  const int q_rows = concept_tile ? p.C : min(kBM, PT - q_row0);
+  const KeySegs ks = key_segments(p, concept_tile);
+  const int n0 = tiles_of(ks.s0, ks.e0), n_tiles = n0 + tiles_of(ks.s1, ks.e1);
+
+  if (tid == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.bar_q, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.bar_k[i], 1); mbar_init(&sm.bar_v[i], 1); }
+    mbar_init(&sm.bar_s, 1); mbar_init(&sm.bar_o, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) { tmem_alloc(&sm.tmem_base, 256); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+  const uint32_t t_s = tmem, t_o = tmem + 128;
+  const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+
+  auto load_k = [&](int j) {
+    int row0, valid; key_tile(ks, n0, j, row0, valid);
+    mbar_expect_tx(&sm.bar_k[j & 1], kTileBytes);
+    tma_load_3d(sm.k[j & 1], &tmk, &sm.bar_k[j & 1], 0, row0, bh);
+    tma_load_3d(sm.k[j & 1] + kHalfBytes, &tmk, &sm.bar_k[j & 1], 64, row0, bh);
+  };
+  auto load_v = [&](int j) {
+    int row0, valid; key_tile(ks, n0, j, row0, valid);
+    mbar_expect_tx(&sm.bar_v[j & 1], kTileBytes);
+    tma_load_3d(sm.v[j & 1], &tmv, &sm.bar_v[j & 1], 0, row0, bh);
+    tma_load_3d(sm.v[j & 1] + kHalfBytes, &tmv, &sm.bar_v[j & 1], 64, row0, bh);
+  };
+  if (tid == 0) {
+    mbar_expect_tx(&sm.bar_q, kTileBytes);
+    tma_load_3d(sm.q, &tmq, &sm.bar_q, 0, q_row0, bh);
+    tma_load_3d(sm.q + kHalfBytes, &tmq, &sm.bar_q, 64, q_row0, bh);
+    load_k(0); load_v(0);
+  }
+
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  float m_used = -INFINITY, l_sum = 0.f;
+
+  for (int j = 0; j < n_tiles; ++j) {
+    const int st = j & 1;
+    int row0, valid; key_tile(ks, n0, j, row0, valid);
+    if (tid == 0) {
+      if (j == 0) mbar_wait(&sm.bar_q, 0);
+      mbar_wait(&sm.bar_k[st], (j >> 1) & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < kD / 16; ++kk) {
+        const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+        mma_ss(t_s, make_smem_desc(smem_u32(sm.q) + off, 16, 1024),
+               make_smem_desc(smem_u32(sm.k[st]) + off, 16, 1024), idesc_qk, kk > 0);
+      }
+      mma_commit(&sm.bar_s);
+    }
+    mbar_wait(&sm.bar_s, j & 1);
+    tc_fence_after();
+    if (tid == 0 && j + 1 < n_tiles) load_k(j + 1);     // K stage st^1 was released by QK(j-1)
+
+    // ---- softmax of this thread's row -------------------------------------------
+    float s[kBN];
+#pragma unroll
+    for (int c = 0; c < kBN; c += 32) {
+      uint32_t r[32];
+      tmem_ld32(t_s + lane_off + c, r);
+      tmem_wait_ld();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) s[c + i] = __uint_as_float(r[i]);
+    }
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < kBN; ++c) { if (c >= valid) s[c] = -INFINITY; mx = fmaxf(mx, s[c]); }
+    const bool grow = (mx - m_used) * p.scale_log2 > kRescaleThreshold;   // also true when m_used = -inf
+    const float m_new = grow ? mx : m_used;
+    const float alpha = grow ? ex2((m_used - m_new) * p.scale_log2) : 1.f;
+    const bool warp_rescale = __any_sync(0xffffffffu, grow);
+
+    if (j > 0) {                                   // PV(j-1) done: O and the P tile are free
+      mbar_wait(&sm.bar_o, (j - 1) & 1);
+      tc_fence_after();
+      if (tid == 0 && j + 1 < n_tiles) load_v(j + 1);
+      if (warp_rescale) {
+#pragma unroll
+        for (int c = 0; c < kD; c += 32) {
+          uint32_t r[32];
+          tmem_ld32(t_o + lane_off + c, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st32(t_o + lane_off + c, r);
+        }
+        tmem_wait_st();
+      }
+    } else if (tid == 0 && n_tiles > 1) {
+      load_v(1);
+    }
+    m_used = m_new;
+    l_sum *= alpha;
+    const float mb = m_used * p.scale_log2;
+    float rs = 0.f;
+#pragma unroll
+    for (int c8 = 0; c8 < kBN / 8; ++c8) {
+      float e[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { e[i] = ex2(s[c8 * 8 + i] * p.scale_log2 - mb); rs += e[i]; }
+      st_swizzled_chunk(sm.p, tid, c8, pack8(e));
+    }
+    l_sum += rs;
+    fence_proxy_async_smem();                       // generic-proxy P writes -> async proxy (MMA)
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      mbar_wait(&sm.bar_v[st], (j >> 1) & 1);
+#pragma unroll
+      for (int kk = 0; kk < kBN / 16; ++kk) {
+        const uint32_t aoff = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+        mma_ss(t_o, make_smem_desc(smem_u32(sm.p) + aoff, 16, 1024),
+               make_smem_desc(smem_u32(sm.v[st]) + kk * 2048, kHalfBytes, 1024), idesc_pv,
+               j > 0 || kk > 0);
+      }
+      mma_commit(&sm.bar_o);
+    }
+  }
+
+  // ---- epilogue: O / l -> bf16 "B L (H D)" -------------------------------------------
+  mbar_wait(&sm.bar_o, (n_tiles - 1) & 1);
+  tc_fence_after();
+  const float inv_l = 1.f / l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + lane_off + c, r);
+    tmem_wait_ld();
+    if (tid < q_rows) {
+      float o[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+      store_out_row(p, b, h, q_row0 + tid, o, inv_l, c, 32);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+// CA_ATTN_NEITHER: concept_attn = concept_v  (modified_double_stream_block.py:157-159),
+// i.e. a head-merge copy of the concept rows of V.
+__global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnParams p) {
+  const int Ntot = p.P + p.T + p.C;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // one 16-byte chunk each
+  const int64_t total = (int64_t)p.B * p.H * p.C * (kD / 8);
+  if (i >= total) return;
+  const int ch = (int)(i % (kD / 8));
+  const int c = (int)((i / (kD / 8)) % p.C);
+  const int h = (int)((i / ((kD / 8) * p.C)) % p.H);
+  const int b = (int)(i / ((int64_t)(kD / 8) * p.C * p.H));
+  const uint4 val = *reinterpret_cast<const uint4*>(
+      v + (((int64_t)b * p.H + h) * Ntot + p.P + p.T + c) * kD + ch * 8);
+  *reinterpret_cast<uint4*>(p.out_txtc + ((int64_t)b * (p.T + p.C) + p.T + c) * p.H * kD + h * kD +
+                            ch * 8) = val;
+}
+
+// ---- host side -------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+// [B*H, Ntot, 128] bf16 viewed as a 3-D tensor; box = 64 x box_rows x 1, 128B swizzle.
+static ca_status make_qkv_tmap(CUtensorMap* m, const void* base, int BH, int Ntot, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return CA_ERR_CUDA;
+  const cuuint64_t dims[3] = {(cuuint64_t)kD, (cuuint64_t)Ntot, (cuuint64_t)BH};
+  const cuuint64_t strides[2] = {(cuuint64_t)kD * 2, (cuuint64_t)Ntot * kD * 2};
+  const cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { g_last_cuda_error = (int)r; return CA_ERR_CUDA; }
+  return CA_OK;
+}
+
+int g_attention_impl = 0;    // 0 = best available, 1 = force v0 (debug / A-B tests)
+
+}  // namespace ca
+
+extern "C" void ca_debug_set_attention_impl(int impl) { ca::g_attention_impl = impl; }
+
+extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void* v, int B, int H,
+                                        int P, int T, int C, int mode, void* out_img,
+                                        void* out_txtc, void* stream) {
+  using namespace ca;
+  if (!q || !k || !v || B < 0 || H <= 0 || P < 0 || T < 0 || C < 0) return CA_ERR_INVALID_ARG;
+  if (mode < CA_ATTN_BOTH || mode > CA_ATTN_NEITHER) return CA_ERR_INVALID_ARG;
+  if (C > CA_MAX_CONCEPTS) return CA_ERR_UNSUPPORTED;
+  if ((P > 0 && !out_img) || (T + C > 0 && !out_txtc)) return CA_ERR_INVALID_ARG;
+  const void* ptrs[] = {q, k, v, out_img, out_txtc};
+  for (const void* ptr : ptrs) if (ptr && !aligned16(ptr)) return CA_ERR_ALIGNMENT;
+  const int Ntot = P + T + C;
+  if (B == 0 || Ntot == 0) return CA_OK;
+  if ((int64_t)B * H > 65535) return CA_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  AttnParams p;
+  p.B = B; p.H = H; p.P = P; p.T = T; p.C = C; p.mode = mode;
+  p.n_main_tiles = (P + T + kBM - 1) / kBM;
+  p.out_img = (__nv_bfloat16*)out_img;
+  p.out_txtc = (__nv_bfloat16*)out_txtc;
+  p.scale_log2 = kLog2e / sqrtf((float)kD);
+
+  CUtensorMap tmq, tmk, tmv;
+  ca_status s;
+  if ((s = make_qkv_tmap(&tmq, q, B * H, Ntot, kBM)) != CA_OK) return s;
+  if ((s = make_qkv_tmap(&tmk, k, B * H, Ntot, kBN)) != CA_OK) return s;
+  if ((s = make_qkv_tmap(&tmv, v, B * H, Ntot, kBN)) != CA_OK) return s;
+
+  const bool concept_attn = C > 0 && mode != CA_ATTN_NEITHER;
+  const int units = p.n_main_tiles + (concept_attn ? 1 : 0);
+  if (units > 0) {
+    const int smem = (int)sizeof(SmemV0) + 1024;
+    CA_CUDA_OK(cudaFuncSetAttribute(attn_v0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attn_v0_kernel<<<dim3(units, B * H), 128, smem, st>>>(tmq, tmk, tmv, p);
+    CA_LAUNCH_CHECK();
+  }
+  if (C > 0 && mode == CA_ATTN_NEITHER) {
+    const int64_t total = (int64_t)B * H * C * (kD / 8);
+    concept_v_copy_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>((const __nv_bfloat16*)v, p);
+    CA_LAUNCH_CHECK();
+  }
+  return CA_OK;
+}

@@ -1,0 +1,272 @@
+"""B200 engine for the concept-aware Flux DiT.
+
+Host-side mirror of `ModifiedFluxDiT` / `ModifiedDoubleStreamBlock`
+(concept_attention/modified_flux_dit.py:29-163,
+concept_attention/modified_double_stream_block.py:43-204) with the same forward
+contract and state-dict keys, re-planned for one B200:
+
+* tokens of one image live in two buffers, `img [B,P,D]` and `txtc [B,T+C,D]`
+  (text rows then concept rows).  Concepts share every txt-stream weight, so
+  each txt GEMM also carries the C concept rows and the weight is read once;
+  only the modulation vector differs per row segment (K1 kernels select it).
+* the big linears are cuBLAS calls through torch (library GEMMs, not claimed);
+  everything between them is one C-ABI kernel: LN+modulate (K1a), split +
+  QK-RMSNorm + RoPE + layout (K1b), one-way joint attention (K2, tcgen05),
+  heatmap logits+softmax+accumulate (K3/K4), gated residual + LN (K1c).
+* the reference's four [Nt,L,B,...] vector stacks are never materialised: a
+  `HeatmapAccumulator` consumes each selected layer's vectors in place.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+from . import _cabi, ops
+from .weights import FluxParams
+
+BF16 = torch.bfloat16
+VECTOR_KEYS = ("output_space_concept_vectors", "output_space_image_vectors",
+               "cross_attention_concept_vectors", "cross_attention_image_vectors")
+
+
+def attention_mode(joint_attention_kwargs) -> int:
+    """joint_attention_kwargs -> CA_ATTN_* (modified_double_stream_block.py:126-159)."""
+    if joint_attention_kwargs is None:
+        return _cabi.ATTN_BOTH
+    cross = joint_attention_kwargs.get("concept_cross_attention", True)
+    self_ = joint_attention_kwargs.get("concept_self_attention", True)
+    if cross and self_:
+        return _cabi.ATTN_BOTH
+    if cross:
+        return _cabi.ATTN_CROSS_ONLY
+    if self_:
+        return _cabi.ATTN_SELF_ONLY
+    return _cabi.ATTN_NEITHER
+
+
+class HeatmapAccumulator:
+    """Running form of compute_heatmaps_from_vectors
+    (concept_attention/concept_attention_pipeline.py:29-91).
+
+    softmax (or sparsemax / entmax15) is applied per (timestep, layer) and the
+    results are averaged over the selected pairs, exactly as :64-82, but pair by
+    pair as the blocks run.  State: fp32 [2, B, C, P] (output space, cross space).
+    """
+
+    def __init__(self, B, C, P, device, layer_indices, timesteps=None, softmax=True,
+                 attention_norm="sparsemax", round_bf16=False, per_pair=False):
+        if not (softmax or attention_norm in ("softmax", "entmax15", "sparsemax")):
+            raise ValueError(f"Unknown attention_norm={attention_norm}")
+        self.norm = "softmax" if (softmax or attention_norm == "softmax") else attention_norm
+        self.layers = [int(i) for i in layer_indices]
+        self.timesteps = None if timesteps is None else [int(t) for t in timesteps]
+        self.round_bf16 = round_bf16
+        self.B, self.C, self.P = B, C, P
+        self.acc = torch.zeros(2, B, C, P, device=device, dtype=torch.float32)
+        self.count = 0
+        self.step = 0
+        self.per_pair = {} if per_pair else None      # (t, l) -> [2,B,C,P]
+
+    def begin_step(self, step_index: int):
+        self.step = step_index
+
+    def multiplicity(self, layer: int) -> int:
+        mt = 1 if self.timesteps is None else self.timesteps.count(self.step)
+        return mt * self.layers.count(layer)
+
+    def add(self, layer, attn_img, attn_con, q_pre, P, T):
+        """attn_img [B,P,D]; attn_con [B,C,D] view; q_pre [B,H,P+T+C,128]."""
+        m = self.multiplicity(layer)
+        if m == 0:
+            return
+        targets = [self.acc] * m
+        if self.per_pair is not None:
+            slot = torch.zeros_like(self.acc)
+            self.per_pair[(self.step, layer)] = slot
+            targets.append(slot)
+        for acc in targets:
+            ops.heatmap_accumulate(attn_img, attn_con, acc[0], self.norm, self.round_bf16)
+            ops.heatmap_accumulate(q_pre[:, :, :P], q_pre[:, :, P + T:], acc[1], self.norm,
+                                   self.round_bf16, per_head=True)
+        self.count += m
+
+    def finalize(self):
+        """-> (concept_heatmaps, cross_attention_maps), each [B,C,h,w] fp32."""
+        if self.count == 0:
+            raise ValueError("no (timestep, layer) pair was selected")
+        out = ops.finalize_heatmaps(self.acc.view(2 * self.B, self.C, self.P), self.count,
+                                    self.round_bf16)
+        out = out.view(2, self.B, self.C, *out.shape[2:])
+        return out[0], out[1]
+
+
+def timestep_embedding(t, dim, max_period=10000, time_factor=1000.0):
+    """flux/src/flux/modules/layers.py:28-49 (cos | sin halves, fp32 then cast)."""
+    t = time_factor * t
+    half = dim // 2
+    freqs = torch.exp(-math.log(max_period) *
+                      torch.arange(half, dtype=torch.float32, device=t.device) / half)
+    args = t[:, None].float() * freqs[None]
+    emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+    return emb.to(t) if torch.is_floating_point(t) else emb
+
+
+def rope_cos_sin(ids, axes_dim, theta):
+    """ids [N,A] -> fp32 [N, sum(axes)/2, 2] (cos, sin); angles in fp64 like
+    flux/src/flux/math.py:15-22."""
+    parts = []
+    for a, dim in enumerate(axes_dim):
+        expo = torch.arange(0, dim, 2, dtype=torch.float64, device=ids.device) / dim
+        omega = 1.0 / (float(theta) ** expo)
+        parts.append(ids[:, a].to(torch.float64)[:, None] * omega[None, :])
+    ang = torch.cat(parts, dim=1)
+    return torch.stack([torch.cos(ang), torch.sin(ang)], dim=-1).float().contiguous()
+
+
+class FluxDiTEngine:
+    """Concept-aware Flux DiT on one B200.  `state_dict` uses the reference keys
+    (see weights.linear_shapes); tensors must be bf16 on `device`."""
+
+    def __init__(self, params: FluxParams, state_dict: dict, device="cuda:0"):
+        self.p = params
+        self.device = torch.device(device)
+        lib = _cabi.load()
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        _cabi.check(lib.ca_device_check(idx), "ca_device_check")
+        D = params.hidden_size
+        if D // params.num_heads != 128 or sum(params.axes_dim) != 128:
+            raise ValueError("the sm_100a attention kernel is built for head_dim 128")
+        self.sd = {}
+        for k, v in state_dict.items():
+            v = v.to(device=self.device, dtype=BF16).contiguous()
+            self.sd[k] = v
+        # linear2 of the single blocks consumes cat(attn, gelu(mlp)); keep its two
+        # column blocks as separate contiguous matrices so no cat is ever built.
+        for i in range(params.depth_single_blocks):
+            w = self.sd.pop(f"single_blocks.{i}.linear2.weight")
+            self.sd[f"single_blocks.{i}.linear2a.weight"] = w[:, :D].contiguous()
+            self.sd[f"single_blocks.{i}.linear2b.weight"] = w[:, D:].contiguous()
+        self._rope_cache = {}
+
+    # -- helpers ---------------------------------------------------------------------
+    def _lin(self, prefix, x):
+        return F.linear(x, self.sd[prefix + ".weight"], self.sd.get(prefix + ".bias"))
+
+    def _mlp_embed(self, prefix, x):
+        return self._lin(prefix + ".out_layer", F.silu(self._lin(prefix + ".in_layer", x)))
+
+    def _rope(self, img_ids, txt_ids, concept_ids):
+        """cos/sin table for the packed order [img | txt | concept]; ids are taken
+        from batch element 0 (prepare()/embed_concepts() repeat them per batch).
+        Cached per id tensors so a denoising loop builds it once."""
+        parts = (img_ids[0], txt_ids[0], concept_ids[0])
+        key = tuple((t.data_ptr(), tuple(t.shape), t._version, str(t.device)) for t in parts)
+        if self._rope_cache.get("key") != key:
+            ids = torch.cat([t.to(self.device, torch.float32) for t in parts], 0)
+            # keep the id tensors alive so data_ptr cannot be recycled under the key
+            self._rope_cache = {"key": key, "ids": parts,
+                                "table": rope_cos_sin(ids, self.p.axes_dim, self.p.theta)}
+        return self._rope_cache["table"]
+
+    # -- forward -----------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, img, img_ids, txt, txt_ids, concepts, concept_ids, concept_vec, timesteps, y,
+                guidance=None, stop_after_multimodal_attentions=False, edit_metadata=None,
+                iteration=None, joint_attention_kwargs=None, accumulator: HeatmapAccumulator = None,
+                collect_vectors=True, **kwargs):
+        """Same contract as ModifiedFluxDiT.forward (modified_flux_dit.py:75-163):
+        returns (pred | None, {key: [L,B,...]}).  With `collect_vectors=False` the
+        dict is empty and heatmaps only flow into `accumulator` (the fast path)."""
+        assert concept_vec is not None, "Concept vectors must be provided for this implementation."
+        if img.ndim != 3 or txt.ndim != 3:
+            raise ValueError("Input img and txt tensors must have 3 dimensions.")
+        p, dev = self.p, self.device
+        D, H = p.hidden_size, p.num_heads
+        to = lambda t: t.to(device=dev, dtype=BF16)
+        img, txt, concepts, y, concept_vec = map(to, (img, txt, concepts, y, concept_vec))
+        timesteps = to(timesteps)
+        B, P, T, C = img.shape[0], img.shape[1], txt.shape[1], concepts.shape[1]
+        mode = attention_mode(joint_attention_kwargs)
+
+        def cond(pooled):
+            v = self._mlp_embed("time_in", timestep_embedding(timesteps, 256))
+            if p.guidance_embed:
+                if guidance is None:
+                    raise ValueError("Didn't get guidance strength for guidance distilled model.")
+                v = v + self._mlp_embed("guidance_in", timestep_embedding(to(guidance), 256))
+            return v + self._mlp_embed("vector_in", pooled)
+
+        x_img = self._lin("img_in", img).contiguous()
+        vec, cvec = cond(y), cond(concept_vec)
+        txtc = self._lin("txt_in", torch.cat((txt, concepts), 1)).contiguous()   # [B,T+C,D]
+        rope = self._rope(img_ids, txt_ids, concept_ids)
+        svec = F.silu(torch.cat((vec, cvec), 0))                                  # [2B,D]
+
+        collected = {k: [] for k in VECTOR_KEYS} if collect_vectors else None
+        for i in range(p.depth):
+            pre = f"double_blocks.{i}"
+            sel = collect_vectors or (accumulator is not None and accumulator.multiplicity(i) > 0)
+            img_mod = self._lin(pre + ".img_mod.lin", svec[:B])                   # [B,6D]
+            tc_mod = self._lin(pre + ".txt_mod.lin", svec)                        # [2B,6D]
+            txt_mod, con_mod = tc_mod[:B], tc_mod[B:]
+            # LN + modulate, qkv GEMMs (concept rows ride on the txt GEMM)
+            img_qkv = self._lin(pre + ".img_attn.qkv", ops.ln_modulate(x_img, img_mod, None, None, 0, D))
+            tc_qkv = self._lin(pre + ".txt_attn.qkv", ops.ln_modulate(txtc, txt_mod, con_mod, T, 0, D))
+            res = ops.qkv_prep(
+                img_qkv, tc_qkv,
+                (self.sd[pre + ".img_attn.norm.query_norm.scale"], self.sd[pre + ".img_attn.norm.key_norm.scale"]),
+                (self.sd[pre + ".txt_attn.norm.query_norm.scale"], self.sd[pre + ".txt_attn.norm.key_norm.scale"]),
+                rope, H, want_q_pre=sel)
+            q, k, v = res[:3]
+            attn_img, attn_tc = ops.joint_attention(q, k, v, P, T, C, mode)
+            if sel:
+                q_pre = res[3]
+                if accumulator is not None:
+                    accumulator.add(i, attn_img, attn_tc[:, T:], q_pre, P, T)
+                if collect_vectors:
+                    collected["output_space_concept_vectors"].append(attn_tc[:, T:].clone())
+                    collected["output_space_image_vectors"].append(attn_img)
+                    collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
+                    collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
+            # residual updates; concept rows use the txt weights with their own gates
+            for x, attn, m0, m1, split, s in ((x_img, attn_img, img_mod, None, None, "img"),
+                                              (txtc, attn_tc, txt_mod, con_mod, T, "txt")):
+                proj = self._lin(f"{pre}.{s}_attn.proj", attn)
+                h = ops.gate_residual_ln_modulate(x, proj, m0, m1, split, 2 * D, 3 * D, 4 * D)
+                h = self._lin(f"{pre}.{s}_mlp.2", F.gelu(self._lin(f"{pre}.{s}_mlp.0", h), approximate="tanh"))
+                ops.gate_residual_ln_modulate(x, h, m0, m1, split, 5 * D, 0, 0, want_out=False)
+        if collect_vectors:
+            collected = {k: torch.stack(v, 0) for k, v in collected.items()}
+        else:
+            collected = {}
+        if stop_after_multimodal_attentions:
+            return None, collected
+
+        # ---- single-stream blocks over [img | txt] (modified_single_stream_block.py:43-56)
+        x = torch.cat((x_img, txtc[:, :T]), 1).contiguous()                      # [B,P+T,D]
+        N = P + T
+        rope_s = rope[:N].contiguous() if C > 0 else rope
+        M = int(D * p.mlp_ratio)
+        for i in range(p.depth_single_blocks):
+            pre = f"single_blocks.{i}"
+            mod = self._lin(pre + ".modulation.lin", svec[:B])                    # [B,3D]
+            h = self._lin(pre + ".linear1", ops.ln_modulate(x, mod, None, None, 0, D))   # [B,N,3D+M]
+            q, k, v = ops.qkv_prep(h, None, (self.sd[pre + ".norm.query_norm.scale"],
+                                             self.sd[pre + ".norm.key_norm.scale"]), None, rope_s, H)
+            if B == 1:
+                attn = torch.empty(1, N, D, device=dev, dtype=BF16)
+                ops.joint_attention(q, k, v, P, T, 0, _cabi.ATTN_BOTH, attn[:, :P], attn[:, P:])
+            else:
+                attn = torch.cat(ops.joint_attention(q, k, v, P, T, 0), 1)
+            out = F.linear(attn, self.sd[pre + ".linear2a.weight"], self.sd[pre + ".linear2.bias"])
+            out = out.view(-1, D).addmm_(F.gelu(h[..., 3 * D:], approximate="tanh").reshape(-1, M),
+                                         self.sd[pre + ".linear2b.weight"].t()).view(B, N, D)
+            ops.gate_residual_ln_modulate(x, out, mod, None, None, 2 * D, 0, 0, want_out=False)
+        x = x[:, :P].contiguous()
+        ada = self._lin("final_layer.adaLN_modulation.1", svec[:B])               # [B,2D] shift|scale
+        pred = self._lin("final_layer.linear", ops.ln_modulate(x, ada, None, None, 0, D))
+        return pred, collected
+
+    __call__ = forward

@@ -1,0 +1,228 @@
+"""Tensor-level wrappers over the C ABI.  torch is used for device memory and the
+current stream only; every op below is one call into libconceptattention_b200.so.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import _cabi
+from ._cabi import NORM
+from ._cabi import check as _check
+
+
+def check(status, what, n_launch=1):
+    global LAUNCHES
+    LAUNCHES += n_launch
+    _check(status, what)
+
+BF16 = torch.bfloat16
+
+# Instrumentation used by bench.py: number of C-ABI kernel launches, and (when
+# ATTN_EVENTS is a list) a CUDA-event pair around every K2 launch on its stream.
+LAUNCHES = 0
+ATTN_EVENTS = None
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _req(t, dtype, name):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise ValueError(f"{name} must be a CUDA tensor (no CPU path exists)")
+    if t.dtype != dtype:
+        raise ValueError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+def ln_modulate(x, mod0, mod1=None, split=None, shift_off=0, scale_off=None, out=None):
+    """(1+scale)*LN(x)+shift.  x [B,N,D] bf16; mod0/mod1 [B,M] bf16 rows holding the
+    modulation chunks; rows >= split use mod1."""
+    B, N, D = x.shape
+    _req(x, BF16, "x"); _req(mod0, BF16, "mod0")
+    if mod1 is not None:
+        _req(mod1, BF16, "mod1")
+        assert mod1.shape == mod0.shape
+    if out is None:
+        out = torch.empty_like(x)
+    scale_off = D if scale_off is None else scale_off
+    check(_cabi.load().ca_ln_modulate(
+        x.data_ptr(), out.data_ptr(), B, N, D, mod0.data_ptr(),
+        mod1.data_ptr() if mod1 is not None else None, N if split is None else split,
+        mod0.stride(0), shift_off, scale_off, _stream(x)), "ca_ln_modulate")
+    return out
+
+
+def gate_residual_ln_modulate(x, y, mod0, mod1=None, split=None, gate_off=0, shift_off=0,
+                              scale_off=0, out=None, want_out=True):
+    """x += gate*y in place; returns (1+scale)*LN(x)+shift if want_out else None.
+    y may be a column slice of a wider matrix (row stride y.stride(-2))."""
+    B, N, D = x.shape
+    _req(x, BF16, "x"); _req(mod0, BF16, "mod0")
+    assert y.dtype == BF16 and y.is_cuda and y.stride(-1) == 1 and y.shape == x.shape
+    assert y.stride(0) == N * y.stride(1) or B == 1
+    if want_out and out is None:
+        out = torch.empty_like(x)
+    check(_cabi.load().ca_gate_residual_ln_modulate(
+        x.data_ptr(), y.data_ptr(), y.stride(1), out.data_ptr() if want_out else None, B, N, D,
+        mod0.data_ptr(), mod1.data_ptr() if mod1 is not None else None,
+        N if split is None else split, mod0.stride(0), gate_off, shift_off, scale_off,
+        _stream(x)), "ca_gate_residual_ln_modulate")
+    return out if want_out else None
+
+
+def qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope, H, want_q_pre=False):
+    """Split + QK-RMSNorm + RoPE + head-major layout.
+    qkv_a [B,Na,>=3*H*128] (row-strided ok), qkv_b [B,Nb,...] or None;
+    scales_* = (q_scale, k_scale) bf16 [128]; rope fp32 [Na+Nb,64,2].
+    Returns q,k,v [B,H,Na+Nb,128] (+ q_pre)."""
+    B, Na = qkv_a.shape[0], qkv_a.shape[1]
+    Nb = 0 if qkv_b is None else qkv_b.shape[1]
+    for t in (qkv_a, qkv_b):
+        if t is not None:
+            assert t.is_cuda and t.dtype == BF16 and t.stride(-1) == 1
+            assert t.shape[0] == 1 or t.stride(0) == t.shape[1] * t.stride(1)
+    _req(rope, torch.float32, "rope")
+    assert rope.shape == (Na + Nb, 64, 2), rope.shape
+    dev = qkv_a.device
+    q, k, v = (torch.empty(B, H, Na + Nb, 128, device=dev, dtype=BF16) for _ in range(3))
+    q_pre = torch.empty_like(q) if want_q_pre else None
+    sb = scales_b if scales_b is not None else (None, None)
+    check(_cabi.load().ca_qkv_prep(
+        qkv_a.data_ptr(), qkv_a.stride(1), Na,
+        qkv_b.data_ptr() if qkv_b is not None else None,
+        qkv_b.stride(1) if qkv_b is not None else 0, Nb,
+        scales_a[0].data_ptr(), scales_a[1].data_ptr(),
+        sb[0].data_ptr() if sb[0] is not None else None,
+        sb[1].data_ptr() if sb[1] is not None else None,
+        rope.data_ptr(), B, H, q.data_ptr(), k.data_ptr(), v.data_ptr(),
+        q_pre.data_ptr() if want_q_pre else None, _stream(qkv_a)), "ca_qkv_prep")
+    return (q, k, v, q_pre) if want_q_pre else (q, k, v)
+
+
+def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_txtc=None):
+    """One-way joint attention over [img|txt|concept]; returns (out_img [B,P,H*128],
+    out_txtc [B,T+C,H*128])."""
+    for n, t in (("q", q), ("k", k), ("v", v)):
+        _req(t, BF16, n)
+    B, H, N, d = q.shape
+    assert d == 128 and N == P + T + C and k.shape == q.shape and v.shape == q.shape
+    if out_img is None:
+        out_img = torch.empty(B, P, H * 128, device=q.device, dtype=BF16)
+    if out_txtc is None:
+        out_txtc = torch.empty(B, T + C, H * 128, device=q.device, dtype=BF16)
+    ev = None
+    if ATTN_EVENTS is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record()
+    check(_cabi.load().ca_joint_attention(
+        q.data_ptr(), k.data_ptr(), v.data_ptr(), B, H, P, T, C, mode,
+        out_img.data_ptr() if P > 0 else None, out_txtc.data_ptr() if T + C > 0 else None,
+        _stream(q)), "ca_joint_attention")
+    if ev is not None:
+        ev[1].record()
+        ATTN_EVENTS.append((ev, B, P, T, C))
+    return out_img, out_txtc
+
+
+def _hm_strides(img, con, per_head):
+    if per_head:      # img [B,H,P,d] view, con [B,H,C,d] view (last dim contiguous)
+        B, H, P, d = img.shape
+        C = con.shape[2]
+        assert img.stride(3) == 1 and con.stride(3) == 1
+        return (B, P, C, H, d, (img.stride(0), img.stride(1), img.stride(2)),
+                (con.stride(0), con.stride(1), con.stride(2)))
+    B, P, K = img.shape
+    C = con.shape[1]
+    assert img.stride(2) == 1 and con.stride(2) == 1
+    return B, P, C, 1, K, (img.stride(0), 0, img.stride(1)), (con.stride(0), 0, con.stride(1))
+
+
+def heatmap_accumulate(img, con, acc, norm="softmax", round_bf16=False, per_head=False):
+    """acc[b,c,p] += norm_c(<img[b,p,:], con[b,c,:]>).  Views with arbitrary
+    batch/row strides are accepted (no copies)."""
+    assert img.dtype == BF16 and con.dtype == BF16 and img.is_cuda
+    B, P, C, nseg, seg_len, si, sc = _hm_strides(img, con, per_head)
+    _req(acc, torch.float32, "acc")
+    assert acc.shape == (B, C, P)
+    check(_cabi.load().ca_heatmap_accumulate(
+        img.data_ptr(), si[0], si[1], si[2], con.data_ptr(), sc[0], sc[1], sc[2], nseg, seg_len,
+        B, P, C, NORM[norm], int(round_bf16), acc.data_ptr(), _stream(img)), "ca_heatmap_accumulate")
+    return acc
+
+
+def heatmap_logits(img, con, per_head=False, out=None):
+    assert img.dtype == BF16 and con.dtype == BF16 and img.is_cuda
+    B, P, C, nseg, seg_len, si, sc = _hm_strides(img, con, per_head)
+    if out is None:
+        out = torch.empty(B, C, P, device=img.device, dtype=torch.float32)
+    check(_cabi.load().ca_heatmap_logits(
+        img.data_ptr(), si[0], si[1], si[2], con.data_ptr(), sc[0], sc[1], sc[2], nseg, seg_len,
+        B, P, C, out.data_ptr(), _stream(img)), "ca_heatmap_logits")
+    return out
+
+
+def norm_accumulate(logits, acc, norm="softmax", round_bf16=False):
+    _req(logits, torch.float32, "logits"); _req(acc, torch.float32, "acc")
+    B, C, P = logits.shape
+    check(_cabi.load().ca_norm_accumulate(logits.data_ptr(), B, P, C, NORM[norm], int(round_bf16),
+                                          acc.data_ptr(), _stream(logits)), "ca_norm_accumulate")
+    return acc
+
+
+def concept_linear_normalize(con):
+    _req(con, BF16, "con")
+    C, K = con.shape
+    out = torch.empty_like(con)
+    check(_cabi.load().ca_concept_linear_normalize(con.data_ptr(), out.data_ptr(), C, K,
+                                                   _stream(con)), "ca_concept_linear_normalize")
+    return out
+
+
+def finalize_heatmaps(acc, count, round_bf16=False):
+    """mean over the `count` accumulated (t,l) pairs -> [B,C,h,w] fp32."""
+    _req(acc, torch.float32, "acc")
+    B, C, P = acc.shape
+    heat = torch.empty_like(acc)
+    check(_cabi.load().ca_finalize_heatmaps(acc.data_ptr(), heat.data_ptr(), acc.numel(),
+                                            1.0 / count, int(round_bf16), _stream(acc)),
+          "ca_finalize_heatmaps")
+    side = math.isqrt(P)
+    return heat.view(B, C, side, side) if side * side == P else heat
+
+
+def gaussian_blur3(maps):
+    _req(maps, torch.float32, "maps")
+    h, w = maps.shape[-2:]
+    out = torch.empty_like(maps)
+    check(_cabi.load().ca_gaussian_blur3(maps.data_ptr(), out.data_ptr(), maps.numel() // (h * w),
+                                         h, w, _stream(maps)), "ca_gaussian_blur3")
+    return out
+
+
+def argmax_mask(heat, num_background=0, apply_blur=False):
+    """heat [B,C,h,w] fp32 -> int64 [B,h,w]; first index on ties."""
+    _req(heat, torch.float32, "heat")
+    if apply_blur:
+        heat = gaussian_blur3(heat)
+    B, C, h, w = heat.shape
+    mask = torch.empty(B, h, w, device=heat.device, dtype=torch.int64)
+    check(_cabi.load().ca_argmax_mask(heat.data_ptr(), mask.data_ptr(), B, C, h * w,
+                                      num_background, _stream(heat)), "ca_argmax_mask")
+    return mask
+
+
+def binary_masks(heat, apply_blur=False):
+    """heat [...,h,w] fp32 -> bool, coeff > mean_hw(coeff) per map."""
+    _req(heat, torch.float32, "heat")
+    if apply_blur:
+        heat = gaussian_blur3(heat)
+    h, w = heat.shape[-2:]
+    mask = torch.empty(heat.shape, device=heat.device, dtype=torch.uint8)
+    check(_cabi.load().ca_binary_masks(heat.data_ptr(), mask.data_ptr(), heat.numel() // (h * w),
+                                       h * w, _stream(heat)), "ca_binary_masks")
+    return mask.bool()

@@ -1,0 +1,172 @@
+/*
+ * conceptattention_b200.h — C ABI of the B200-native ConceptAttention hot path.
+ *
+ * Drop-in boundary.  The reference (manuragkhullar/ConceptAttention @ 401dc36) is
+ * pure Python/PyTorch and has no FFI; the entry points below are what a ctypes
+ * binding on the reference side would call in place of the PyTorch op sequences
+ * cited on each function (paths under concept_attention/).  INTEGRATION.md shows
+ * that binding.
+ *
+ * Conventions
+ *  - every pointer is a raw DEVICE pointer unless the name ends in _host;
+ *  - activations are bf16 (uint16 storage), accumulators/heatmaps fp32, masks
+ *    int64 / uint8; all tensors dense row-major with the shapes given;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *  - functions never allocate device memory (except *_host wrappers), never
+ *    synchronise (except *_host wrappers) and never throw; they return
+ *    CA_OK or a negative ca_status code.  Thread-safe for disjoint buffers;
+ *  - sm_100a only: on any other device ca_device_check / the kernels' launch
+ *    return CA_ERR_ARCH / CA_ERR_CUDA.  There is no fallback path.
+ *  - token order inside one (batch, head) sequence is [img | txt | concept]:
+ *    N_tot = P + T + C.  Attention is permutation-equivariant, so this differs
+ *    from the reference's cat(txt,img) / cat(concept,img) only in layout.
+ */
+#ifndef CONCEPTATTENTION_B200_H_
+#define CONCEPTATTENTION_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int ca_status;
+enum {
+  CA_OK = 0,
+  CA_ERR_INVALID_ARG = -1,   /* null pointer, negative size, bad enum            */
+  CA_ERR_UNSUPPORTED = -2,   /* shape outside what the kernels are built for    */
+  CA_ERR_ALIGNMENT = -3,     /* pointer / stride not 16-byte aligned            */
+  CA_ERR_ARCH = -4,          /* device is not sm_100                            */
+  CA_ERR_CUDA = -5           /* CUDA runtime/driver error; see ca_last_cuda_error */
+};
+
+#define CA_HEAD_DIM 128      /* Flux head dim (hidden 3072 / 24 heads)           */
+#define CA_MAX_CONCEPTS 32
+
+/* concept_attention_pipeline.py:64-71 */
+enum { CA_NORM_SOFTMAX = 0, CA_NORM_SPARSEMAX = 1, CA_NORM_ENTMAX15 = 2, CA_NORM_NONE = 3 };
+/* modified_double_stream_block.py:126-168 (joint_attention_kwargs ablations) */
+enum { CA_ATTN_BOTH = 0, CA_ATTN_CROSS_ONLY = 1, CA_ATTN_SELF_ONLY = 2, CA_ATTN_NEITHER = 3 };
+
+const char* ca_version(void);
+const char* ca_status_string(ca_status s);
+int ca_last_cuda_error(void);                 /* cudaError_t / CUresult of the last failure */
+ca_status ca_device_check(int device);        /* CA_OK iff compute capability 10.x */
+
+/* ---- K1a: LayerNorm(eps 1e-6, no affine) + adaLN modulate -------------------
+ * out[b,n,:] = (1 + scale) * LN(x[b,n,:]) + shift, fp32 maths, bf16 out.
+ * Rows n <  split take (shift,scale) from mod0[b], rows n >= split from mod1[b]
+ * (concept rows use txt weights but their own modulation vector).
+ * Replaces modified_double_stream_block.py:88-89,94-95,100-101 and
+ * modified_single_stream_block.py:47.  mod rows are bf16 [*, mod_stride];
+ * shift at +shift_off, scale at +scale_off (elements). */
+ca_status ca_ln_modulate(const void* x, void* out, int B, int N, int D,
+                         const void* mod0, const void* mod1, int split,
+                         int64_t mod_stride, int shift_off, int scale_off, void* stream);
+
+/* ---- K1c: gated residual, optionally followed by LN + modulate --------------
+ * x[b,n,:] += gate * (y[b,n,:] (+ 0));  if out != NULL:
+ * out[b,n,:] = (1 + scale2) * LN(x) + shift2.   y has row stride y_stride.
+ * Replaces modified_double_stream_block.py:194-202 (the elementwise parts) and
+ * modified_single_stream_block.py:56. */
+ca_status ca_gate_residual_ln_modulate(void* x, const void* y, int64_t y_stride, void* out,
+                                       int B, int N, int D,
+                                       const void* mod0, const void* mod1, int split,
+                                       int64_t mod_stride, int gate_off, int shift_off,
+                                       int scale_off, void* stream);
+
+/* ---- K1b: qkv split + QK-RMSNorm + RoPE + head-major layout -----------------
+ * qkv_a: bf16 [B, Na, row_stride_a] rows of the image stream (first 3*H*128
+ * columns are "(K H D)"), normalised with (q_scale_a, k_scale_a);
+ * qkv_b: bf16 [B, Nb, row_stride_b] rows of [txt | concept] with (q_scale_b,
+ * k_scale_b); may be NULL with Nb = 0 (single-stream blocks).
+ * rope: fp32 [Na+Nb, 64, 2] = (cos, sin) of the per-token angles
+ * (flux/src/flux/math.py:15-22), token order [a | b].
+ * q,k,v: bf16 [B,H,Na+Nb,128]; q_pre (nullable): post-RMSNorm PRE-RoPE q, the
+ * reference's cross_attention_*_vectors (modified_double_stream_block.py:189-190).
+ * Replaces :91-92,97-98,103-104,110,125 and flux/src/flux/modules/layers.py:63-84,
+ * flux/src/flux/math.py:25-30. */
+ca_status ca_qkv_prep(const void* qkv_a, int64_t row_stride_a, int Na,
+                      const void* qkv_b, int64_t row_stride_b, int Nb,
+                      const void* q_scale_a, const void* k_scale_a,
+                      const void* q_scale_b, const void* k_scale_b,
+                      const float* rope, int B, int H,
+                      void* q, void* k, void* v, void* q_pre, void* stream);
+
+/* ---- K2: one-way joint attention (tcgen05 / TMEM / TMA) ---------------------
+ * q,k,v bf16 [B,H,P+T+C,128], order [img|txt|concept].
+ *   rows [0,P+T)      attend keys [0,P+T)                     (txt (+) img, :106-119)
+ *   rows [P+T,P+T+C)  attend keys [0,P) U [P+T,P+T+C)         (concept (+) img, :121-168)
+ * mode selects the ablation for the concept rows (CA_ATTN_*).  Image rows of the
+ * reference's second attention are never computed.
+ * out_img bf16 [B,P,H*128]; out_txtc bf16 [B,T+C,H*128] ("B L (H D)", :170-176).
+ * softmax scale = 1/sqrt(128).  C may be 0 (single-stream blocks; then T rows
+ * still go to out_txtc). */
+ca_status ca_joint_attention(const void* q, const void* k, const void* v,
+                             int B, int H, int P, int T, int C, int mode,
+                             void* out_img, void* out_txtc, void* stream);
+
+/* ---- K3+K4: heatmap logits + normalise over concepts + accumulate -----------
+ * logits[b,c,p] = sum_{s<nseg} sum_{j<seg_len} img[b,s,p,j] * con[b,s,c,j]
+ * where element (b,s,p,j) sits at img + b*img_stride_b + s*img_stride_s +
+ * p*img_stride_p + j (bf16 elements); same for con with con_stride_{b,s,c}.
+ * Output space: nseg=1, seg_len=H*128; cross-attention space: nseg=H, seg_len=128
+ * (concept_attention_pipeline.py:43-61).
+ * acc[b,c,p] (fp32) += norm_c(logits[b,:,p])  with norm in CA_NORM_* (:64-71);
+ * CA_NORM_NONE accumulates raw logits (multi_class_segmentation.py:59-63).
+ * round_bf16 != 0 reproduces the reference's bf16 rounding points (logits and
+ * probabilities rounded to bf16 before use). */
+ca_status ca_heatmap_accumulate(const void* img, int64_t img_stride_b, int64_t img_stride_s,
+                                int64_t img_stride_p,
+                                const void* con, int64_t con_stride_b, int64_t con_stride_s,
+                                int64_t con_stride_c,
+                                int nseg, int seg_len, int B, int P, int C,
+                                int norm, int round_bf16, float* acc, void* stream);
+
+/* K3 only: partial logits of a head/feature slice, written (not accumulated) as
+ * fp32 [B,C,P] — the buffer a head-sharded run all-reduces before K4. */
+ca_status ca_heatmap_logits(const void* img, int64_t img_stride_b, int64_t img_stride_s,
+                            int64_t img_stride_p,
+                            const void* con, int64_t con_stride_b, int64_t con_stride_s,
+                            int64_t con_stride_c,
+                            int nseg, int seg_len, int B, int P, int C,
+                            float* logits, void* stream);
+
+/* K4 only: acc += norm_c(logits) on fp32 [B,C,P]. */
+ca_status ca_norm_accumulate(const float* logits, int B, int P, int C, int norm,
+                             int round_bf16, float* acc, void* stream);
+
+/* utils.py:35-44 applied over the concept axis of a [C,K] bf16 matrix
+ * (normalize_concepts=True, concept_attention_pipeline.py:53-54). */
+ca_status ca_concept_linear_normalize(const void* con, void* out, int C, int64_t K,
+                                      void* stream);
+
+/* ---- K5: finalise and heatmap -> mask ----------------------------------------
+ * heat = acc * inv_count (mean over selected (t,l), :78-82); optional bf16 rounding. */
+ca_status ca_finalize_heatmaps(const float* acc, float* heat, int64_t n, float inv_count,
+                               int round_bf16, void* stream);
+/* 3x3 gaussian blur sigma=1, reflect padding (segmentation.py:57-58). maps [M,h,w] fp32. */
+ca_status ca_gaussian_blur3(const float* in, float* out, int M, int h, int w, void* stream);
+/* mask[b,p] = argmax_c heat[b,c,p] (first index on ties), indices < num_background -> 0
+ * (multi_class_segmentation.py:77; run_multi_class_seg_experiment.py:25-31). */
+ca_status ca_argmax_mask(const float* heat, int64_t* mask, int B, int C, int P,
+                         int num_background, void* stream);
+/* mask[m,p] = heat[m,p] > mean_p(heat[m,:])   (segmentation.py:60-61). M = B*C maps. */
+ca_status ca_binary_masks(const float* heat, uint8_t* mask, int M, int P, void* stream);
+
+/* ---- host-buffer form of compute_heatmaps_from_vectors (:29-91) --------------
+ * image_host  bf16 [Nt,L,B,P,K]   (or per-head [Nt,L,B,H,P,d] when per_head != 0)
+ * concept_host bf16 [Nt,L,B,C,K]  (or [Nt,L,B,H,C,d])
+ * Selected (timestep, layer) pairs are copied H2D, reduced on the device with
+ * K3+K4+K5 and the [B,C,P] fp32 mean heatmap is copied back.  Synchronises. */
+ca_status ca_heatmaps_from_vectors_host(const void* image_host, const void* concept_host,
+                                        int Nt, int L, int B, int H, int P, int C, int d,
+                                        int per_head, const int* timesteps, int n_timesteps,
+                                        const int* layers, int n_layers, int norm,
+                                        int round_bf16, float* heat_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CONCEPTATTENTION_B200_H_ */

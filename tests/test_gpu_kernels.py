@@ -1,0 +1,172 @@
+"""GPU parity tests, kernel by kernel: every call goes through the C ABI
+(conceptattention_b200.ops -> libconceptattention_b200.so) and is compared with
+the CPU oracle on the same seeded inputs.  Run on the B200 box: pytest -m gpu."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+BF16 = torch.bfloat16
+
+
+@pytest.fixture(scope="module")
+def ops():
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    from conceptattention_b200 import _cabi, ops as _ops
+    _cabi.check(_cabi.load().ca_device_check(0), "device")
+    return _ops
+
+
+def rnd(*shape, seed=0, scale=1.0, dtype=BF16):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dtype)
+
+
+def close(a, b, rtol, atol):
+    torch.testing.assert_close(a.float().cpu(), b.float().cpu(), rtol=rtol, atol=atol)
+
+
+# ---------------------------------------------------------------- K1a / K1c
+@pytest.mark.parametrize("B,N,D,split", [(1, 75, 256, 72), (2, 33, 3072, 30), (1, 260, 3072, 256),
+                                         (1, 5, 1024, None)])
+def test_ln_modulate(ops, B, N, D, split):
+    x = rnd(B, N, D, seed=1, scale=2.0)
+    mod0, mod1 = rnd(B, 6 * D, seed=2, scale=0.5), rnd(B, 6 * D, seed=3, scale=0.5)
+    out = ops.ln_modulate(x.cuda(), mod0.cuda(), None if split is None else mod1.cuda(), split, 0, D)
+    s = N if split is None else split
+    xf = x.float()
+    ref = torch.empty_like(xf)
+    for m, sl in ((mod0, slice(0, s)), (mod1, slice(s, N))):
+        mf = m.float()[:, None, :]
+        ref[:, sl] = oracle.layer_norm_modulate(xf[:, sl], mf[..., :D], mf[..., D:2 * D])
+    close(out, ref, rtol=1e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("B,N,D,split,want_out", [(1, 75, 256, 72, True), (2, 40, 3072, 36, True),
+                                                  (1, 20, 3072, None, False)])
+def test_gate_residual_ln_modulate(ops, B, N, D, split, want_out):
+    x, y = rnd(B, N, D, seed=4), rnd(B, N, D, seed=5)
+    mod0, mod1 = rnd(B, 6 * D, seed=6, scale=0.5), rnd(B, 6 * D, seed=7, scale=0.5)
+    xg = x.cuda().clone()
+    out = ops.gate_residual_ln_modulate(xg, y.cuda(), mod0.cuda(),
+                                        None if split is None else mod1.cuda(), split,
+                                        2 * D, 3 * D, 4 * D, want_out=want_out)
+    s = N if split is None else split
+    xr = x.float().clone()
+    ref = torch.empty_like(xr)
+    for m, sl in ((mod0, slice(0, s)), (mod1, slice(s, N))):
+        mf = m.float()[:, None, :]
+        xr[:, sl] = (xr[:, sl] + mf[..., 2 * D:3 * D] * y.float()[:, sl]).to(BF16).float()
+        ref[:, sl] = oracle.layer_norm_modulate(xr[:, sl], mf[..., 3 * D:4 * D], mf[..., 4 * D:5 * D])
+    close(xg, xr, rtol=1e-2, atol=1e-2)
+    if want_out:
+        close(out, ref, rtol=2e-2, atol=3e-2)
+    else:
+        assert out is None
+
+
+# ---------------------------------------------------------------- K1b
+@pytest.mark.parametrize("B,Na,Nb,H,extra", [(1, 144, 75, 2, 0), (2, 64, 20, 3, 0), (1, 100, 0, 2, 512)])
+def test_qkv_prep(ops, B, Na, Nb, H, extra):
+    D = H * 128
+    qa = rnd(B, Na, 3 * D + extra, seed=8)
+    qb = rnd(B, Nb, 3 * D, seed=9) if Nb else None
+    sc = [(1 + 0.3 * torch.randn(128, generator=torch.Generator().manual_seed(10 + i))).to(BF16)
+          for i in range(4)]
+    side = int(math.ceil(math.sqrt(Na)))
+    ids = torch.zeros(Na + Nb, 3)
+    ids[:Na, 1] = torch.arange(Na) // side
+    ids[:Na, 2] = torch.arange(Na) % side
+    if Nb:
+        ids[Na:Na + 3, 1] = 5.0        # non-zero text ids must rotate too (general path)
+    pe = oracle.rope_table(ids[None], [16, 56, 56], 10000)                  # [1,1,N,64,2,2]
+    table = torch.stack([pe[0, 0, :, :, 0, 0], pe[0, 0, :, :, 1, 0]], -1).contiguous()   # cos, sin
+    res = ops.qkv_prep(qa.cuda(), qb.cuda() if Nb else None, (sc[0].cuda(), sc[1].cuda()),
+                       (sc[2].cuda(), sc[3].cuda()) if Nb else None, table.cuda(), H, want_q_pre=True)
+    q, k, v, q_pre = [t.cpu() for t in res]
+    # oracle, stream by stream
+    qs, ks, vs, qps = [], [], [], []
+    for src, (s_q, s_k) in ((qa[..., :3 * D], (sc[0], sc[1])),) + (((qb, (sc[2], sc[3])),) if Nb else ()):
+        oq, ok, ov = oracle.split_heads(src, H)
+        oq, ok = oracle.rms_norm_qk(oq, ok, ov, s_q, s_k)
+        qs.append(oq); ks.append(ok); vs.append(ov); qps.append(oq)
+    oq, ok, ov, oqp = (torch.cat(t, 2) for t in (qs, ks, vs, qps))
+    oq, ok = oracle.apply_rope(oq, ok, pe)
+    assert torch.equal(v, ov)
+    close(q_pre, oqp, rtol=1e-2, atol=1e-2)
+    close(q, oq, rtol=1e-2, atol=2e-2)
+    close(k, ok, rtol=1e-2, atol=2e-2)
+
+
+# ---------------------------------------------------------------- K2
+def _attention_oracle(q, k, v, P, T, C, mode):
+    """q,k,v [B,H,P+T+C,128] fp32 in packed order -> (img [B,P,HD], txtc [B,T+C,HD])."""
+    PT = P + T
+    main = oracle.sdpa_explicit(q[:, :, :PT], k[:, :, :PT], v[:, :, :PT])
+    outs = [main]
+    if C:
+        cq = q[:, :, PT:]
+        if mode == 0:
+            kk, vv = torch.cat((k[:, :, :P], k[:, :, PT:]), 2), torch.cat((v[:, :, :P], v[:, :, PT:]), 2)
+            outs.append(oracle.sdpa_explicit(cq, kk, vv))
+        elif mode == 1:
+            outs.append(oracle.sdpa_explicit(cq, k[:, :, :P], v[:, :, :P]))
+        elif mode == 2:
+            outs.append(oracle.sdpa_explicit(cq, k[:, :, PT:], v[:, :, PT:]))
+        else:
+            outs.append(v[:, :, PT:])
+    o = oracle.merge_heads(torch.cat(outs, 2))
+    return o[:, :P], o[:, P:]
+
+
+ATTN_CASES = [
+    (1, 2, 144, 72, 3, 0), (1, 2, 144, 72, 3, 1), (1, 2, 144, 72, 3, 2), (1, 2, 144, 72, 3, 3),
+    (2, 3, 256, 256, 4, 0), (1, 2, 1024, 256, 32, 0), (1, 1, 200, 100, 1, 0), (1, 2, 384, 128, 0, 0),
+    (1, 1, 64, 0, 2, 0),
+]
+
+
+@pytest.mark.parametrize("B,H,P,T,C,mode", ATTN_CASES)
+def test_joint_attention(ops, B, H, P, T, C, mode):
+    N = P + T + C
+    q, k, v = rnd(B, H, N, 128, seed=20, scale=1.5), rnd(B, H, N, 128, seed=21), rnd(B, H, N, 128, seed=22)
+    oi, ot = ops.joint_attention(q.cuda(), k.cuda(), v.cuda(), P, T, C, mode)
+    ri, rt = _attention_oracle(q.float(), k.float(), v.float(), P, T, C, mode)
+    close(oi, ri, rtol=2e-2, atol=1e-2)
+    close(ot, rt, rtol=2e-2, atol=1e-2)
+
+
+def test_joint_attention_one_way(ops):
+    """Image and text rows must not depend on the concept tokens at all (bit-exact)."""
+    B, H, P, T, C = 1, 2, 384, 128, 5
+    N = P + T + C
+    q, k, v = (rnd(B, H, N, 128, seed=s) for s in (30, 31, 32))
+    a_i, a_t = ops.joint_attention(q.cuda(), k.cuda(), v.cuda(), P, T, C)
+    q2, k2, v2 = q.clone(), k.clone(), v.clone()
+    for t in (q2, k2, v2):
+        t[:, :, P + T:] = rnd(B, H, C, 128, seed=33, scale=3.0)
+    b_i, b_t = ops.joint_attention(q2.cuda(), k2.cuda(), v2.cuda(), P, T, C)
+    assert torch.equal(a_i, b_i) and torch.equal(a_t[:, :T], b_t[:, :T])
+    assert not torch.equal(a_t[:, T:], b_t[:, T:])
+
+
+@pytest.mark.parametrize("P,T,C,H", [(4096, 256, 4, 24)])
+def test_joint_attention_full_size_properties(ops, P, T, C, H):
+    """BASELINE config-2 shape: V = 1 -> every output is 1 (softmax rows sum to 1), and two
+    heads are checked against the oracle."""
+    N = P + T + C
+    q, k = rnd(1, H, N, 128, seed=40), rnd(1, H, N, 128, seed=41)
+    ones = torch.ones(1, H, N, 128, dtype=BF16)
+    oi, ot = ops.joint_attention(q.cuda(), k.cuda(), ones.cuda(), P, T, C)
+    assert (oi.float() - 1).abs().max() < 8e-3 and (ot.float() - 1).abs().max() < 8e-3
+    v = rnd(1, H, N, 128, seed=42)
+    oi, ot = ops.joint_attention(q.cuda(), k.cuda(), v.cuda(), P, T, C)
+    hs = [0, H - 1]
+    ri, rt = _attention_oracle(q[:, hs].float(), k[:, hs].float(), v[:, hs].float(), P, T, C, 0)
+    for j, h in enumerate(hs):
+        close(oi[..., h * 128:(h + 1) * 128], ri[..., j * 128:(j + 1) * 128], rtol=2e-2, atol=5e-3)
+        close(ot[..., h * 128:(h + 1) * 128], rt[..., j * 128:(j + 1) * 128], rtol=2e-2, atol=5e-3)
