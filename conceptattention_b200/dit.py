@@ -162,7 +162,12 @@ class FluxDiTEngine:
         from batch element 0 (prepare()/embed_concepts() repeat them per batch).
         Cached per id tensors so a denoising loop builds it once."""
         parts = (img_ids[0], txt_ids[0], concept_ids[0])
-        key = tuple((t.data_ptr(), tuple(t.shape), t._version, str(t.device)) for t in parts)
+        def ver(t):                       # inference tensors have no version counter
+            try:
+                return t._version
+            except RuntimeError:
+                return -1
+        key = tuple((t.data_ptr(), tuple(t.shape), ver(t), str(t.device)) for t in parts)
         if self._rope_cache.get("key") != key:
             ids = torch.cat([t.to(self.device, torch.float32) for t in parts], 0)
             # keep the id tensors alive so data_ptr cannot be recycled under the key

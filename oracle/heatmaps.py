@@ -77,6 +77,8 @@ def heatmaps_from_vectors(image_vectors, concept_vectors, layer_indices, timeste
     maps = maps[list(timesteps)][:, list(layer_indices)]
     maps = maps.mean(dim=(0, 1))
     side = math.isqrt(maps.shape[-1])
+    if side * side != maps.shape[-1]:                   # non-square token count: keep [B,C,P]
+        return maps
     return maps.reshape(*maps.shape[:-1], side, side)
 
 
