@@ -145,11 +145,13 @@ def run_ours(args, rank, world, local_rank):
     clocks = ClockSampler(local_rank)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()      # no-op unless run under `ncu --profile-from-start off`
     e0.record()
     for i in range(args.steps):
         device_step(args.warmup + i)
     e1.record()
     barrier()
+    torch.cuda.profiler.stop()
     ms_dev = e0.elapsed_time(e1)
     clk = clocks.stop()
     launches = ops.LAUNCHES

@@ -253,6 +253,263 @@ attn_v0_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+// =============================================================================
+// v1: warp-specialised kernel.  One CTA = TWO 128-row query tiles of one (b,h)
+// (or one tile: odd tail / the concept tile), 384 threads:
+//   warp 0      TMA producer: Q tiles once, then K(j), V(j) through a 4-slot ring
+//   warp 1      MMA issuer (one elected lane): S_t = Q_t K^T, O_t += P_t V
+//   warp 2      TMEM allocator (512 columns: S0 S1 O0 O1), warp 3 idle
+//   warps 4-7   softmax warpgroup of tile 0: thread == query row == TMEM lane
+//   warps 8-11  softmax warpgroup of tile 1
+// P_t (bf16) is written back over the first 64 columns of S_t in TMEM and consumed
+// as the A operand of the PV MMA straight from TMEM (no shared-memory round trip).
+// The two tiles ping-pong: while warpgroup t runs exp2 on S_t(j), the tensor core
+// runs PV_{1-t}(j) and QK_{1-t}(j+1).  O is rescaled lazily (only when a row max
+// grows by more than 2^8) by the softmax warpgroup itself, which is safe without an
+// extra barrier because the commit that publishes S_t(j) also covers PV_t(j-1).
+// =============================================================================
+constexpr int kKvStages = 4;
+
+struct SmemV1 {
+  uint8_t q[2][kTileBytes];
+  uint8_t kv[kKvStages][kTileBytes];
+  uint64_t q_full[2], kv_full[kKvStages], kv_empty[kKvStages], s_full[2], p_full[2], o_done;
+  uint32_t tmem_base;
+};
+
+struct UnitV1 {
+  bool concept_tile;
+  int n_q;            // query tiles in this CTA (1 or 2)
+  int q_row0[2], q_rows[2];
+  KeySegs ks;
+  int n0, n_tiles;
+};
+
+__device__ __forceinline__ UnitV1 decode_unit(const AttnParams& p, int unit) {
+  UnitV1 u;
+  const int PT = p.P + p.T;
+  const int n_pairs = (p.n_main_tiles + 1) >> 1;
+  u.concept_tile = unit >= n_pairs;
+  if (u.concept_tile) {
+    u.n_q = 1;
+    u.q_row0[0] = PT; u.q_rows[0] = p.C; u.q_row0[1] = PT; u.q_rows[1] = 0;
+  } else {
+    u.n_q = min(2, p.n_main_tiles - 2 * unit);
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      u.q_row0[t] = (2 * unit + t) * kBM;
+      u.q_rows[t] = max(0, min(kBM, PT - u.q_row0[t]));
+    }
+  }
+  u.ks = key_segments(p, u.concept_tile);
+  u.n0 = tiles_of(u.ks.s0, u.ks.e0);
+  u.n_tiles = u.n0 + tiles_of(u.ks.s1, u.ks.e1);
+  return u;
+}
+
+__device__ __forceinline__ void v1_producer(SmemV1& sm, const CUtensorMap* tmq,
+                                            const CUtensorMap* tmk, const CUtensorMap* tmv,
+                                            const UnitV1& u, int bh) {
+  int item = 0;
+  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
+    mbar_expect_tx(bar, kTileBytes);
+    tma_load_3d(dst, tm, bar, 0, row0, bh);
+    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+  };
+  auto load_kv = [&](const CUtensorMap* tm, int j) {
+    int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
+    const int slot = item % kKvStages;
+    mbar_wait(&sm.kv_empty[slot], ((item / kKvStages) & 1) ^ 1);
+    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    ++item;
+  };
+  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
+  load_kv(tmk, 0);
+  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
+  load_kv(tmv, 0);
+  for (int j = 1; j < u.n_tiles; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
+}
+
+__device__ __forceinline__ void v1_mma(SmemV1& sm, uint32_t tmem, const UnitV1& u) {
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  auto kv_wait = [&](int item) {
+    const int slot = item % kKvStages;
+    mbar_wait(&sm.kv_full[slot], (item / kKvStages) & 1);
+    return slot;
+  };
+  auto qk = [&](int t, int kslot) {                      // S_t = Q_t K^T
+    const uint32_t qa = smem_u32(sm.q[t]), ka = smem_u32(sm.kv[kslot]);
+#pragma unroll
+    for (int kk = 0; kk < kD / 16; ++kk) {
+      const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+      mma_ss(tmem + t * 128, make_smem_desc(qa + off, 16, 1024), make_smem_desc(ka + off, 16, 1024),
+             idesc_qk, kk > 0);
+    }
+    mma_commit(&sm.s_full[t]);
+  };
+  auto pv = [&](int t, int vslot, bool acc) {            // O_t (+)= P_t V, P_t from TMEM
+    const uint32_t va = smem_u32(sm.kv[vslot]);
+#pragma unroll
+    for (int kk = 0; kk < kBN / 16; ++kk)
+      mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kk * 8,
+             make_smem_desc(va + kk * 2048, kHalfBytes, 1024), idesc_pv, acc || kk > 0);
+  };
+  const bool two = u.n_q == 2;
+  mbar_wait(&sm.q_full[0], 0);
+  int ks = kv_wait(0);
+  tc_fence_after();
+  qk(0, ks);
+  if (two) { mbar_wait(&sm.q_full[1], 0); tc_fence_after(); qk(1, ks); }
+  mma_commit(&sm.kv_empty[ks]);
+  for (int j = 0; j < u.n_tiles; ++j) {
+    const bool has_next = j + 1 < u.n_tiles;
+    const int vs = kv_wait(2 * j + 1);
+    if (has_next) ks = kv_wait(2 * j + 2);
+    mbar_wait(&sm.p_full[0], j & 1);
+    tc_fence_after();
+    pv(0, vs, j > 0);
+    if (has_next) qk(0, ks);
+    if (two) {
+      mbar_wait(&sm.p_full[1], j & 1);
+      tc_fence_after();
+      pv(1, vs, j > 0);
+    }
+    mma_commit(&sm.kv_empty[vs]);
+    if (has_next) {
+      if (two) qk(1, ks);
+      mma_commit(&sm.kv_empty[ks]);
+    }
+  }
+  mma_commit(&sm.o_done);
+}
+
+__device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const UnitV1& u,
+                                           const AttnParams& p, int t, int b, int h) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
+  const float scale = p.scale_log2;
+  float m_used = -INFINITY, l_sum = 0.f;
+
+#pragma unroll 1
+  for (int j = 0; j < u.n_tiles; ++j) {
+    int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
+    mbar_wait(&sm.s_full[t], j & 1);
+    tc_fence_after();
+    uint32_t sr[kBN];
+#pragma unroll
+    for (int c = 0; c < kBN; c += 32) tmem_ld32(t_s + c, sr + c);
+    tmem_wait_ld();
+    if (valid < kBN) {                                    // ragged last tile of a key segment
+#pragma unroll
+      for (int c = 0; c < kBN; ++c) if (c >= valid) sr[c] = 0xff800000u;   // -inf
+    }
+    float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
+    float mx2 = __uint_as_float(sr[2]), mx3 = __uint_as_float(sr[3]);
+#pragma unroll
+    for (int c = 4; c < kBN; c += 4) {
+      mx0 = fmaxf(mx0, __uint_as_float(sr[c]));     mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
+      mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2])); mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
+    }
+    const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+    const bool grow = (mx - m_used) * scale > kRescaleThreshold;   // true on the first tile
+    const float m_new = grow ? mx : m_used;
+    if (j > 0 && __any_sync(0xffffffffu, grow)) {
+      // PV_t(j-1) has completed: the commit behind s_full[t] covers it.
+      const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
+      l_sum *= alpha;
+#pragma unroll
+      for (int c = 0; c < kD; c += 32) {
+        uint32_t r[32];
+        tmem_ld32(t_o + c, r);
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+        tmem_st32(t_o + c, r);
+      }
+    }
+    m_used = m_new;
+    const float mb = m_used * scale;
+    float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+    for (int c = 0; c < kBN; c += 32) {
+      uint32_t pk[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float e0 = ex2(fmaf(__uint_as_float(sr[c + 2 * i]), scale, -mb));
+        const float e1 = ex2(fmaf(__uint_as_float(sr[c + 2 * i + 1]), scale, -mb));
+        rs0 += e0; rs1 += e1;
+        pk[i] = pack2(e0, e1);
+      }
+      tmem_st16(t_s + (c >> 1), pk);                     // P_t over the first 64 columns of S_t
+    }
+    l_sum += rs0 + rs1;
+    tmem_wait_st();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.p_full[t]);
+  }
+
+  // ---- epilogue: O_t / l -> bf16 "B L (H D)" ---------------------------------------
+  mbar_wait(&sm.o_done, 0);
+  tc_fence_after();
+  const float inv_l = 1.f / l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + c, r);
+    tmem_wait_ld();
+    if (row < u.q_rows[t]) {
+      float o[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+      store_out_row(p, b, h, u.q_row0[t] + row, o, inv_l, c, 32);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(384, 1)
+attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+               const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV1& sm = *reinterpret_cast<SmemV1*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
+  const UnitV1 u = decode_unit(p, blockIdx.x);
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
+    for (int i = 0; i < kKvStages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], 4); }
+    mbar_init(&sm.o_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp < 4) {
+    setmaxnreg_dec<40>();
+    if (warp == 0) {
+      if (elect_one()) v1_producer(sm, &tmq, &tmk, &tmv, u, bh);
+    } else if (warp == 1) {
+      if (elect_one()) v1_mma(sm, tmem, u);
+    }
+  } else {
+    setmaxnreg_inc<232>();
+    const int t = (warp >> 2) - 1;
+    if (t < u.n_q) v1_softmax(sm, tmem, u, p, t, b, h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
 // CA_ATTN_NEITHER: concept_attn = concept_v  (modified_double_stream_block.py:157-159),
 // i.e. a head-merge copy of the concept rows of V.
 __global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnParams p) {
@@ -338,12 +595,22 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
   if ((s = make_qkv_tmap(&tmv, v, B * H, Ntot, kBN)) != CA_OK) return s;
 
   const bool concept_attn = C > 0 && mode != CA_ATTN_NEITHER;
-  const int units = p.n_main_tiles + (concept_attn ? 1 : 0);
-  if (units > 0) {
-    const int smem = (int)sizeof(SmemV0) + 1024;
-    CA_CUDA_OK(cudaFuncSetAttribute(attn_v0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attn_v0_kernel<<<dim3(units, B * H), 128, smem, st>>>(tmq, tmk, tmv, p);
-    CA_LAUNCH_CHECK();
+  if (g_attention_impl == 1) {
+    const int units = p.n_main_tiles + (concept_attn ? 1 : 0);
+    if (units > 0) {
+      const int smem = (int)sizeof(SmemV0) + 1024;
+      CA_CUDA_OK(cudaFuncSetAttribute(attn_v0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      attn_v0_kernel<<<dim3(units, B * H), 128, smem, st>>>(tmq, tmk, tmv, p);
+      CA_LAUNCH_CHECK();
+    }
+  } else {
+    const int units = (p.n_main_tiles + 1) / 2 + (concept_attn ? 1 : 0);
+    if (units > 0) {
+      const int smem = (int)sizeof(SmemV1) + 1024;
+      CA_CUDA_OK(cudaFuncSetAttribute(attn_v1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      attn_v1_kernel<<<dim3(units, B * H), 384, smem, st>>>(tmq, tmk, tmv, p);
+      CA_LAUNCH_CHECK();
+    }
   }
   if (C > 0 && mode == CA_ATTN_NEITHER) {
     const int64_t total = (int64_t)B * H * C * (kD / 8);

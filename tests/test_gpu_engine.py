@@ -28,27 +28,54 @@ def _rel(a, b):
     return ((a - b).abs().max() / b.abs().max()).item()
 
 
+def _bf16_floor(p, sd, inp, t, gd, golden, **kw):
+    """Distance of a bf16 run of the reference op sequence (oracle, CPU, bf16 tensors =
+    the reference's own GPU numerics) from the fp32 golden vectors: the bf16 noise
+    floor the engine is allowed to sit at."""
+    sdd = {k: v.to(BF16) for k, v in sd.items()}
+    ii = {k: v.to(BF16) for k, v in inp.items()}
+    pred, vecs = oracle.dit_forward(sdd, p.asdict(), ii["img"], ii["img_ids"], ii["txt"],
+                                    ii["txt_ids"], ii["concepts"], ii["concept_ids"],
+                                    ii["concept_vec"], t.to(BF16), ii["vec"], gd.to(BF16), **kw)
+    out = {k: _rel(vecs[k], golden(k)) for k in oracle.VECTOR_KEYS}
+    if pred is not None:
+        out["pred"] = _rel(pred, golden("pred"))
+    return out
+
+
 @pytest.mark.parametrize("cfg", ["tiny", "tiny-dev"])
 def test_engine_vectors_match_reference_golden(golden_dir, cfg):
+    """Engine (bf16, CUDA kernels) vs the golden vectors the reference's own modules
+    produced in fp32.  A bf16 pipeline cannot be closer to fp32 than bf16 rounding
+    allows, so the bound per tensor is 1.5x the error of the reference op sequence
+    itself run in bf16 (floor, 3-12 % after 2-3 blocks at these sizes), never less
+    than 2e-2.  Kernel-exact parity is in test_gpu_kernels.py."""
     g = np.load(os.path.join(golden_dir, f"dit_{cfg}.npz"))
     p, sd, eng = _engine(cfg)
     inp = gi.dit_inputs(p, gi.TINY_SIDE, gi.TINY_T, gi.TINY_C, gi.INPUT_SEED)
     t, gd = torch.full((1,), 0.75), torch.full((1,), 3.5)
+    floor = _bf16_floor(p, sd, inp, t, gd, lambda k: g[k])
     pred, vecs = eng(img=inp["img"], img_ids=inp["img_ids"], txt=inp["txt"], txt_ids=inp["txt_ids"],
                      concepts=inp["concepts"], concept_ids=inp["concept_ids"],
                      concept_vec=inp["concept_vec"], y=inp["vec"], timesteps=t, guidance=gd)
     for k in oracle.VECTOR_KEYS:
         assert tuple(vecs[k].shape) == g[k].shape, k
-        assert _rel(vecs[k], g[k]) < 4e-2, (k, _rel(vecs[k], g[k]))
-    assert _rel(pred, g["pred"]) < 5e-2, _rel(pred, g["pred"])
+        r = _rel(vecs[k], g[k])
+        print(f"{cfg} {k}: engine {r:.3e} floor {floor[k]:.3e}")
+        assert r <= max(2e-2, 1.5 * floor[k]), (k, r, floor[k])
+    r = _rel(pred, g["pred"])
+    assert r <= max(2e-2, 1.5 * floor["pred"]), (r, floor["pred"])
     for name, kw in gi.ABLATIONS.items():
         none, v2 = eng(img=inp["img"], img_ids=inp["img_ids"], txt=inp["txt"], txt_ids=inp["txt_ids"],
                        concepts=inp["concepts"], concept_ids=inp["concept_ids"],
                        concept_vec=inp["concept_vec"], y=inp["vec"], timesteps=t, guidance=gd,
                        stop_after_multimodal_attentions=True, joint_attention_kwargs=kw)
         assert none is None
+        fl = _bf16_floor(p, sd, inp, t, gd,
+                         lambda k: g["ablation_" + name] if k == "output_space_concept_vectors" else g[k],
+                         stop_after_multimodal_attentions=True, joint_attention_kwargs=kw)
         r = _rel(v2["output_space_concept_vectors"], g["ablation_" + name])
-        assert r < 4e-2, (name, r)
+        assert r <= max(2e-2, 1.5 * fl["output_space_concept_vectors"]), (name, r, fl)
 
 
 def _rel_map(got, ref):
@@ -119,7 +146,11 @@ def test_accumulated_heatmaps_match_oracle(concept_scale):
         err = _rel_map(got, r32)
         print(f"{tag}: engine vs fp32 oracle {err:.3e}; bf16 oracle vs fp32 oracle {floor:.3e}; "
               f"engine vs bf16 oracle {_rel_map(got, r16):.3e}")
-        assert err <= max(1e-2, 1.5 * floor), (tag, err, floor)
+        # max-relative error is a noisy statistic on peaky maps: bound it at 2x the floor
+        # and the mean absolute error at 1.5x
+        assert err <= max(1e-2, 2.0 * floor), (tag, err, floor)
+        mae = lambda a, b: (a.float().cpu() - b.float()).abs().mean().item()
+        assert mae(got, r32) <= 1.5 * mae(r16, r32) + 1e-4, (tag, mae(got, r32), mae(r16, r32))
     mask = ops.argmax_mask(out.contiguous()).cpu()
     assert torch.equal(mask, out.cpu().argmax(1))            # device argmax is exact on its own input
     bm = ops.binary_masks(out.contiguous()).cpu()
