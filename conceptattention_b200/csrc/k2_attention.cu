@@ -16,6 +16,7 @@
 // tracked with mbarriers; MMA completion is signalled with tcgen05.commit.
 #include "ca_common.cuh"
 #include "sm100_ptx.cuh"
+#include "tma_host.cuh"
 
 namespace ca {
 
@@ -528,23 +529,6 @@ __global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnP
 }
 
 // ---- host side -------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
-                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (fn) return fn;
-  void* sym = nullptr;
-  cudaDriverEntryPointQueryResult qres;
-  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
-      qres != cudaDriverEntryPointSuccess)
-    return nullptr;
-  fn = reinterpret_cast<EncodeTiledFn>(sym);
-  return fn;
-}
-
 // [B*H, Ntot, 128] bf16 viewed as a 3-D tensor; box = 64 x box_rows x 1, 128B swizzle.
 static ca_status make_qkv_tmap(CUtensorMap* m, const void* base, int BH, int Ntot, int box_rows) {
   EncodeTiledFn enc = get_encode_fn();

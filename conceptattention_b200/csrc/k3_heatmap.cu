@@ -11,77 +11,11 @@
 //    acc[b,c,p] (coalesced across the R rows of neighbouring warps per concept).
 // The 4 x [Nt,L,B,...] stacks of the reference (a8 in SURVEY.md) never exist.
 #include "ca_common.cuh"
+#include "heatmap_norm.cuh"
 
 namespace ca {
 
 constexpr int kHmWarps = 8;
-
-template <int CT>
-__device__ __forceinline__ void normalise(float (&z)[CT], int C, int norm, bool round_bf16) {
-  if (round_bf16) {
-#pragma unroll
-    for (int c = 0; c < CT; ++c) z[c] = bf16_round(z[c]);
-  }
-  if (norm == CA_NORM_NONE) return;
-  float m = -INFINITY;
-#pragma unroll
-  for (int c = 0; c < CT; ++c) if (c < C) m = fmaxf(m, z[c]);
-  if (norm == CA_NORM_SOFTMAX) {
-    float s = 0.f;
-#pragma unroll
-    for (int c = 0; c < CT; ++c) { z[c] = (c < C) ? __expf(z[c] - m) : 0.f; s += z[c]; }
-    const float inv = 1.f / s;
-#pragma unroll
-    for (int c = 0; c < CT; ++c) z[c] *= inv;
-  } else {
-    // Sort-free O(C^2) threshold search (C <= 32).  For element i let
-    // k_i = #{z_j >= z_i}, s_i = sum of those, q_i = sum of their squares.
-    const bool ent = (norm == CA_NORM_ENTMAX15);
-    if (ent) {
-#pragma unroll
-      for (int c = 0; c < CT; ++c) z[c] = (z[c] - m) * 0.5f;
-    }
-    float tau = 0.f, best_k = 0.f;
-#pragma unroll
-    for (int i = 0; i < CT; ++i) {
-      if (i < C) {
-        float k = 0.f, s = 0.f, q = 0.f;
-#pragma unroll
-        for (int j = 0; j < CT; ++j) {
-          if (j < C && z[j] >= z[i]) { k += 1.f; s += z[j]; q += z[j] * z[j]; }
-        }
-        float t;
-        bool in_support;
-        if (!ent) {                       // sparsemax: 1 + k z_i > s
-          t = (s - 1.f) / k;
-          in_support = 1.f + k * z[i] > s;
-        } else {                          // entmax-1.5 (Peters et al. 2019, Alg. 2)
-          const float mean = s / k, msq = q / k;
-          const float delta = fmaxf((1.f - k * (msq - mean * mean)) / k, 0.f);
-          t = mean - sqrtf(delta);
-          in_support = t <= z[i];
-        }
-        if (in_support && k > best_k) { best_k = k; tau = t; }
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < CT; ++c) {
-      const float d = (c < C) ? fmaxf(z[c] - tau, 0.f) : 0.f;
-      z[c] = ent ? d * d : d;
-    }
-  }
-  if (round_bf16) {
-#pragma unroll
-    for (int c = 0; c < CT; ++c) z[c] = bf16_round(z[c]);
-  }
-}
-
-struct HmArgs {
-  const __nv_bfloat16* img; int64_t isb, iss, isp;
-  const __nv_bfloat16* con; int64_t csb, css, csc;
-  int nseg, seg_len, B, P, C, norm, round_bf16;
-  float* acc;      // fused: acc += norm(logits);   logits-only: acc = logits
-};
 
 template <int R, int CT, bool kLogitsOnly>
 __global__ void __launch_bounds__(kHmWarps * 32)
@@ -149,8 +83,11 @@ heatmap_kernel(const HmArgs a) {
         for (int c = 0; c < CT; ++c) if (c < a.C) dst[(int64_t)c * a.P] = sum[r][c];
       } else {
         normalise<CT>(sum[r], a.C, a.norm, a.round_bf16 != 0);
+        float old[CT];                       // all loads before the first store (no serialised RMW)
 #pragma unroll
-        for (int c = 0; c < CT; ++c) if (c < a.C) dst[(int64_t)c * a.P] += sum[r][c];
+        for (int c = 0; c < CT; ++c) old[c] = c < a.C ? __ldcg(dst + (int64_t)c * a.P) : 0.f;
+#pragma unroll
+        for (int c = 0; c < CT; ++c) if (c < a.C) dst[(int64_t)c * a.P] = old[c] + sum[r][c];
       }
     }
   }
@@ -166,9 +103,12 @@ __global__ void norm_accumulate_kernel(const float* __restrict__ logits, float* 
   float z[CT];
 #pragma unroll
   for (int c = 0; c < CT; ++c) z[c] = c < C ? logits[((int64_t)b * C + c) * P + p] : 0.f;
+  float old[CT];
+#pragma unroll
+  for (int c = 0; c < CT; ++c) old[c] = c < C ? __ldcg(acc + ((int64_t)b * C + c) * P + p) : 0.f;
   normalise<CT>(z, C, norm, round_bf16 != 0);
 #pragma unroll
-  for (int c = 0; c < CT; ++c) if (c < C) acc[((int64_t)b * C + c) * P + p] += z[c];
+  for (int c = 0; c < CT; ++c) if (c < C) acc[((int64_t)b * C + c) * P + p] = old[c] + z[c];
 }
 
 // Column-wise min-shift / sum normalisation of a [C,K] bf16 matrix (utils.py:35-44).
@@ -186,6 +126,8 @@ __global__ void concept_linear_normalize_kernel(const __nv_bfloat16* __restrict_
     out[c * K + k] = __float2bfloat16_rn(bf16_round(__bfloat162float(in[c * K + k]) - mn) / s);
 }
 
+int g_heatmap_impl = 0;      // 0 = best available, 1 = force the SIMT kernel (debug / A-B tests)
+
 template <bool kLogitsOnly>
 static ca_status launch_heatmap(const HmArgs& a, cudaStream_t st) {
   if (!a.img || !a.con || !a.acc || a.B < 0 || a.P < 0 || a.C <= 0 || a.nseg <= 0 || a.seg_len <= 0)
@@ -195,6 +137,10 @@ static ca_status launch_heatmap(const HmArgs& a, cudaStream_t st) {
   if (!aligned16(a.img) || !aligned16(a.con) || (a.isb | a.iss | a.isp | a.csb | a.css | a.csc) % 8)
     return CA_ERR_ALIGNMENT;
   if (a.B == 0 || a.P == 0) return CA_OK;
+  if (g_heatmap_impl != 1) {          // TMA/tcgen05 streaming variant when the shape fits it
+    const ca_status s = launch_heatmap_tc(a, kLogitsOnly, st);
+    if (s != CA_ERR_UNSUPPORTED) return s;
+  }
   const size_t smem = (size_t)a.C * a.nseg * a.seg_len * 2;
   if (smem > 220 * 1024) return CA_ERR_UNSUPPORTED;
 #define CA_HM_LAUNCH(R, CT)                                                                     \
@@ -215,6 +161,8 @@ static ca_status launch_heatmap(const HmArgs& a, cudaStream_t st) {
 }
 
 }  // namespace ca
+
+extern "C" void ca_debug_set_heatmap_impl(int impl) { ca::g_heatmap_impl = impl; }
 
 extern "C" ca_status ca_heatmap_accumulate(const void* img, int64_t isb, int64_t iss, int64_t isp,
                                            const void* con, int64_t csb, int64_t css, int64_t csc,

@@ -52,6 +52,30 @@ def test_heatmap_accumulate(ops, norm, B, P, C, K):
     torch.testing.assert_close(acc.cpu(), ref, rtol=2e-4, atol=2e-4)
 
 
+@pytest.mark.parametrize("B,P,C,K", [(1, 4096, 4, 3072), (2, 1000, 20, 3072), (1, 300, 32, 1024),
+                                     (3, 129, 16, 128), (1, 16384, 32, 3072)])
+def test_heatmap_tc_matches_simt_and_oracle(ops, B, P, C, K):
+    """The TMA/tcgen05 streaming kernel (cluster split-K, DSMEM reduce) and the SIMT kernel
+    compute the same maps; both match the oracle."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    iv, cv = rnd(B, P, K, seed=11), rnd(B, C, K, seed=12, scale=3.0 / math.sqrt(K))
+    out = []
+    try:
+        for impl in (0, 1):
+            lib.ca_debug_set_heatmap_impl(impl)
+            acc = torch.zeros(B, C, P, device="cuda")
+            ops.heatmap_accumulate(iv.cuda(), cv.cuda(), acc, "softmax")
+            logits = ops.heatmap_logits(iv.cuda(), cv.cuda())
+            out.append((acc.cpu(), logits.cpu()))
+    finally:
+        lib.ca_debug_set_heatmap_impl(0)
+    torch.testing.assert_close(out[0][0], out[1][0], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(out[0][1], out[1][1], rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(out[0][0], _oracle_maps(iv, cv, "softmax", False), rtol=2e-4, atol=2e-4)
+    torch.testing.assert_close(out[0][1], _oracle_maps(iv, cv, "none", False), rtol=2e-4, atol=2e-4)
+
+
 @pytest.mark.parametrize("norm", ["softmax", "sparsemax"])
 def test_heatmap_accumulate_per_head_strided(ops, norm):
     """cross-attention space: per-head vectors read in place from a [B,H,N,128] buffer."""
