@@ -92,6 +92,22 @@ class HeatmapAccumulator:
                                    self.round_bf16, per_head=True)
         self.count += m
 
+    def add_logits(self, layer, logits):
+        """Head-sharded form: `logits` fp32 [2,B,C,P] (output space, cross space) are the
+        all-reduced sums of the ranks' partial logits; normalise + accumulate (K4)."""
+        m = self.multiplicity(layer)
+        if m == 0:
+            return
+        targets = [self.acc] * m
+        if self.per_pair is not None:
+            slot = torch.zeros_like(self.acc)
+            self.per_pair[(self.step, layer)] = slot
+            targets.append(slot)
+        for acc in targets:
+            for s in range(2):
+                ops.norm_accumulate(logits[s], acc[s], self.norm, self.round_bf16)
+        self.count += m
+
     def finalize(self):
         """-> (concept_heatmaps, cross_attention_maps), each [B,C,h,w] fp32."""
         if self.count == 0:
@@ -129,9 +145,13 @@ class FluxDiTEngine:
     """Concept-aware Flux DiT on one B200.  `state_dict` uses the reference keys
     (see weights.linear_shapes); tensors must be bf16 on `device`."""
 
-    def __init__(self, params: FluxParams, state_dict: dict, device="cuda:0"):
+    def __init__(self, params: FluxParams, state_dict: dict, device="cuda:0", head_shard=None):
+        """`head_shard` (parallel.HeadShard): this rank computes only its head slice of the
+        double-stream attention (qkv GEMM rows, K1b, K2, K3 partial logits); attention
+        outputs are all-gathered over heads, partial heatmap logits all-reduced."""
         self.p = params
         self.device = torch.device(device)
+        self.hs = head_shard
         lib = _cabi.load()
         idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
         _cabi.check(lib.ca_device_check(idx), "ca_device_check")
@@ -148,6 +168,14 @@ class FluxDiTEngine:
             w = self.sd.pop(f"single_blocks.{i}.linear2.weight")
             self.sd[f"single_blocks.{i}.linear2a.weight"] = w[:, :D].contiguous()
             self.sd[f"single_blocks.{i}.linear2b.weight"] = w[:, D:].contiguous()
+        if self.hs is not None and self.hs.world > 1:
+            rows = self.hs.qkv_rows(128).to(self.device)
+            for i in range(params.depth):
+                for st in ("img", "txt"):
+                    for kind in ("weight", "bias"):
+                        key = f"double_blocks.{i}.{st}_attn.qkv.{kind}"
+                        if key in self.sd:
+                            self.sd[key] = self.sd[key][rows].contiguous()
         self._rope_cache = {}
 
     # -- helpers ---------------------------------------------------------------------
@@ -219,22 +247,33 @@ class FluxDiTEngine:
             # LN + modulate, qkv GEMMs (concept rows ride on the txt GEMM)
             img_qkv = self._lin(pre + ".img_attn.qkv", ops.ln_modulate(x_img, img_mod, None, None, 0, D))
             tc_qkv = self._lin(pre + ".txt_attn.qkv", ops.ln_modulate(txtc, txt_mod, con_mod, T, 0, D))
+            Hl = H if self.hs is None else self.hs.h_local
             res = ops.qkv_prep(
                 img_qkv, tc_qkv,
                 (self.sd[pre + ".img_attn.norm.query_norm.scale"], self.sd[pre + ".img_attn.norm.key_norm.scale"]),
                 (self.sd[pre + ".txt_attn.norm.query_norm.scale"], self.sd[pre + ".txt_attn.norm.key_norm.scale"]),
-                rope, H, want_q_pre=sel)
+                rope, Hl, want_q_pre=sel)
             q, k, v = res[:3]
             attn_img, attn_tc = ops.joint_attention(q, k, v, P, T, C, mode)
-            if sel:
-                q_pre = res[3]
-                if accumulator is not None:
-                    accumulator.add(i, attn_img, attn_tc[:, T:], q_pre, P, T)
+            q_pre = res[3] if sel else None
+            if self.hs is not None and self.hs.world > 1:
+                if sel and accumulator is not None and accumulator.multiplicity(i) > 0:
+                    # partial logits over this rank's heads, ONE all-reduce for both spaces
+                    part = torch.empty(2, B, C, P, device=dev, dtype=torch.float32)
+                    ops.heatmap_logits(attn_img, attn_tc[:, T:], out=part[0])
+                    ops.heatmap_logits(q_pre[:, :, :P], q_pre[:, :, P + T:], per_head=True, out=part[1])
+                    accumulator.add_logits(i, self.hs.all_reduce_sum(part))
+                attn_img = self.hs.all_gather_heads(attn_img)
+                attn_tc = self.hs.all_gather_heads(attn_tc)
                 if collect_vectors:
-                    collected["output_space_concept_vectors"].append(attn_tc[:, T:].clone())
-                    collected["output_space_image_vectors"].append(attn_img)
-                    collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
-                    collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
+                    q_pre = self.hs.all_gather(q_pre, 1)
+            elif sel and accumulator is not None:
+                accumulator.add(i, attn_img, attn_tc[:, T:], q_pre, P, T)
+            if sel and collect_vectors:
+                collected["output_space_concept_vectors"].append(attn_tc[:, T:].clone())
+                collected["output_space_image_vectors"].append(attn_img)
+                collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
+                collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
             # residual updates; concept rows use the txt weights with their own gates
             for x, attn, m0, m1, split, s in ((x_img, attn_img, img_mod, None, None, "img"),
                                               (txtc, attn_tc, txt_mod, con_mod, T, "txt")):

@@ -1,0 +1,141 @@
+"""Multi-GPU plumbing: one process per GPU over torch.distributed (NCCL on the GPU
+box, gloo in the CPU tests).
+
+Two modes:
+
+* data parallel by image / prompt — the default.  Images are independent (the
+  reference is batch-1, single GPU: concept_attention/image_generator.py:135-142), so
+  a work list is split round-robin over ranks, every rank runs its own pipeline with
+  replicated weights, and the ONLY communication is the final gather of the small
+  per-image results.  No collective on the data path.
+* head sharding — for very large token counts.  Attention is independent per head
+  and the heatmap logits are a plain sum over H*d (concept_attention_pipeline.py:57-61),
+  hence over heads; softmax over concepts is not linear so it comes after the sum.
+  `HeadShard` describes a rank's head slice and carries the two collectives the path
+  needs: all-gather of attention outputs over heads, all-reduce(SUM) of partial logits.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+
+def init_distributed(backend: str | None = None):
+    """Initialise the default process group from the torchrun environment.
+    Returns (rank, world_size, local_rank).  Single process: no group is created."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        kw = {}
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+            kw["device_id"] = torch.device("cuda", local_rank)
+        dist.init_process_group(backend, rank=rank, world_size=world, **kw)
+    return rank, world, local_rank
+
+
+def shard_indices(n_items: int, rank: int, world: int) -> list[int]:
+    """Round-robin partition of range(n_items): item i goes to rank i % world."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world of {world}")
+    return list(range(rank, n_items, world))
+
+
+def gather_results(local: torch.Tensor, n_items: int, rank: int, world: int, dst: int = 0,
+                   group=None):
+    """Collect per-item results of a round-robin sharded run on `dst`.
+
+    local: [len(shard_indices(n_items, rank, world)), ...] on any device.  Returns
+    [n_items, ...] in the ORIGINAL item order on rank `dst` (None elsewhere).  Shards
+    are padded to ceil(n_items / world) so one fixed-size gather suffices."""
+    if world == 1:
+        return local
+    per = (n_items + world - 1) // world
+    mine = len(shard_indices(n_items, rank, world))
+    if local.shape[0] != mine:
+        raise ValueError(f"rank {rank}: expected {mine} local results, got {local.shape[0]}")
+    pad = torch.zeros((per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    pad[:mine] = local
+    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == dst else None
+    dist.gather(pad, bufs, dst=dst, group=group)
+    if rank != dst:
+        return None
+    out = torch.empty((n_items,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    for r in range(world):
+        idx = shard_indices(n_items, r, world)
+        if idx:
+            out[idx] = bufs[r][:len(idx)]
+    return out
+
+
+@dataclass
+class HeadShard:
+    """Head slice [h0, h1) of rank `rank` among `world` ranks plus the collectives of
+    the head-sharded path.  `group=None` uses the default process group."""
+    rank: int
+    world: int
+    num_heads: int
+    group: object = None
+
+    def __post_init__(self):
+        if self.num_heads % self.world:
+            raise ValueError(f"{self.num_heads} heads do not split over {self.world} ranks")
+        self.h_local = self.num_heads // self.world
+        self.h0 = self.rank * self.h_local
+        self.h1 = self.h0 + self.h_local
+
+    # -- weight slicing -------------------------------------------------------------
+    def qkv_rows(self, head_dim: int = 128) -> torch.Tensor:
+        """Row indices of a fused qkv weight [(K H D), in] that produce this rank's heads,
+        ordered (K, H_local, D) so the sliced GEMM output is again '(K H D)'."""
+        D = self.num_heads * head_dim
+        cols = torch.arange(self.h0 * head_dim, self.h1 * head_dim)
+        return torch.cat([cols + k * D for k in range(3)])
+
+    # -- collectives ------------------------------------------------------------------
+    def _gloo(self) -> bool:
+        """gloo (CPU tests, and the 2-process single-GPU test) has no CUDA / flat all_gather:
+        use the list form and stage CUDA tensors through the host.  NCCL runs on device."""
+        return dist.get_backend(self.group) == "gloo"
+
+    def all_gather(self, x: torch.Tensor, dim: int) -> torch.Tensor:
+        """Concatenate the ranks' `x` along `dim` in rank order.  Bit-exact: pure data movement."""
+        if self.world == 1:
+            return x
+        x = x.contiguous()
+        if self._gloo():
+            parts = [torch.empty(x.shape, dtype=x.dtype) for _ in range(self.world)]
+            dist.all_gather(parts, x.cpu(), group=self.group)
+            return torch.cat(parts, dim=dim).to(x.device)
+        out = torch.empty((self.world,) + tuple(x.shape), dtype=x.dtype, device=x.device)
+        dist.all_gather_into_tensor(out, x, group=self.group)
+        nd = x.dim()
+        dim = dim % nd
+        # [G, d0.., dim, ..] -> [d0.., G, dim, ..] -> merge (G, dim)
+        perm = list(range(1, dim + 1)) + [0] + list(range(dim + 1, nd + 1))
+        shape = list(x.shape)
+        shape[dim] *= self.world
+        return out.permute(*perm).reshape(shape)
+
+    def all_gather_heads(self, x: torch.Tensor) -> torch.Tensor:
+        """x [..., H_local*d] (this rank's heads) -> [..., H*d] with heads in rank order."""
+        return self.all_gather(x, -1)
+
+    def all_reduce_sum(self, x: torch.Tensor) -> torch.Tensor:
+        """In-place SUM over ranks (partial heatmap logits, fp32)."""
+        if self.world > 1:
+            if self._gloo() and x.is_cuda:
+                h = x.cpu()
+                dist.all_reduce(h, op=dist.ReduceOp.SUM, group=self.group)
+                x.copy_(h)
+            else:
+                dist.all_reduce(x, op=dist.ReduceOp.SUM, group=self.group)
+        return x

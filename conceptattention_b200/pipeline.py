@@ -69,7 +69,7 @@ class FluxGenerator:
     concept_attention/image_generator.py:64-205."""
 
     def __init__(self, model_name="flux-schnell", device="cuda:0", offload=False,
-                 state_dict=None, seed=0, t5=None, clip=None, ae=None):
+                 state_dict=None, seed=0, t5=None, clip=None, ae=None, head_shard=None):
         self.device = torch.device(device)
         self.offload = offload
         self.model_name = model_name
@@ -78,7 +78,7 @@ class FluxGenerator:
         if state_dict is None:
             state_dict = init_state_dict(self.params, seed=seed, device=self.device,
                                          dtype=torch.bfloat16)
-        self.model = FluxDiTEngine(self.params, state_dict, device=self.device)
+        self.model = FluxDiTEngine(self.params, state_dict, device=self.device, head_shard=head_shard)
         self.t5 = t5 or sampling.SyntheticEmbedder(self.params.context_in_dim,
                                                    T5_MAX_LENGTH[model_name], self.device)
         self.clip = clip or sampling.SyntheticEmbedder(self.params.vec_in_dim, None, self.device)
@@ -145,13 +145,13 @@ class ConceptAttentionFluxPipeline:
     and default to the reference behaviour."""
 
     def __init__(self, model_name: str = "flux-schnell", offload_model=False, device="cuda:0",
-                 state_dict=None, seed=0, t5=None, clip=None, ae=None):
+                 state_dict=None, seed=0, t5=None, clip=None, ae=None, head_shard=None):
         self.model_name = model_name
         self.offload_model = offload_model
         _cabi.load()                      # fail loudly before any weights are built
         self.flux_generator = FluxGenerator(model_name=model_name, offload=offload_model,
                                             device=device, state_dict=state_dict, seed=seed,
-                                            t5=t5, clip=clip, ae=ae)
+                                            t5=t5, clip=clip, ae=ae, head_shard=head_shard)
 
     # ------------------------------------------------------------------------------
     @torch.no_grad()
