@@ -30,13 +30,30 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 METRIC = "concept-heatmap images/sec @1024^2 Flux-schnell"
+CONCEPT_WORDS = ["dragon", "rock", "sky", "sun", "tree", "grass", "cloud", "river", "bird", "stone",
+                 "water", "fire", "snow", "sand", "road", "wall", "roof", "door", "lamp", "boat",
+                 "fish", "leaf", "hill", "moon", "star", "rain", "wind", "path", "gate", "pond",
+                 "reed", "moss"]
 WORKLOADS = {
-    # name: model, side, concepts, steps, layers
-    "schnell-1024": dict(model="flux-schnell", side=1024, C=4, nsteps=4, layers=list(range(15, 19))),
-    "tiny-256": dict(model="tiny", side=256, C=4, nsteps=2, layers=[1, 2]),     # debug only
+    # BASELINE.json configs[1] — the bench line.  mode generate: one step = one image.
+    "schnell-1024": dict(model="flux-schnell", side=1024, C=4, nsteps=4, layers=list(range(15, 19)),
+                         mode="generate", batch=1),
+    # configs[2]: encode_image segmentation sweep, one noised timestep, 19 double blocks only;
+    # one step = one batch of `batch` 512x512 images per GPU (data parallel).
+    "encode-512": dict(model="flux-schnell", side=512, C=2, nsteps=4, layers=list(range(15, 19)),
+                       mode="encode", batch=16),
+    # configs[3]: flux-dev architecture, 20 concepts, 28 steps, per-layer AND per-timestep maps
+    "dev-1024-c20": dict(model="flux-dev", side=1024, C=20, nsteps=28, layers=list(range(19)),
+                         mode="generate", batch=1, per_pair=True, guidance=3.5),
+    # configs[4]: 2048^2, 32 concepts, heads sharded over the ranks (strong scaling: all ranks
+    # work on the same image; needs WORLD_SIZE dividing 24)
+    "schnell-2048-hs": dict(model="flux-schnell", side=2048, C=32, nsteps=4, layers=list(range(15, 19)),
+                            mode="generate", batch=1, head_shard=True),
+    "tiny-256": dict(model="tiny", side=256, C=4, nsteps=2, layers=[1, 2], mode="generate", batch=1),
 }
 D_HEAD = 128
 
@@ -102,23 +119,34 @@ def attention_flops(P, T, C, H, double):
 def run_ours(args, rank, world, local_rank):
     from conceptattention_b200 import ConceptAttentionFluxPipeline, ops, sampling
     from conceptattention_b200.dit import HeatmapAccumulator
+    from conceptattention_b200.parallel import HeadShard, gather_results
     wl = WORKLOADS[args.config]
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     side, C, nsteps, layers = wl["side"], wl["C"], wl["nsteps"], wl["layers"]
-    concepts = ["dragon", "rock", "sky", "sun", "tree", "grass", "cloud", "river"][:C]
+    mode, batch = wl["mode"], wl["batch"]
+    sharded = bool(wl.get("head_shard")) and world > 1
+    guidance = wl.get("guidance", 0.0)
+    concepts = CONCEPT_WORDS[:C]
     prompt = "A dragon standing on a rock"
-    # text encoders on the HOST (pinned) so the e2e arm pays the H2D copy of their outputs
-    pipe = ConceptAttentionFluxPipeline(model_name=wl["model"], device=dev, seed=rank)
+    # head-sharded ranks hold the SAME weights and work on the same image; DP ranks differ
+    hs = None
+    if sharded:
+        from conceptattention_b200.weights import CONFIGS
+        hs = HeadShard(rank, world, CONFIGS[wl["model"]].num_heads)
+    pipe = ConceptAttentionFluxPipeline(model_name=wl["model"], device=dev, seed=0 if sharded else rank,
+                                        head_shard=hs)
     gen = pipe.flux_generator
     pm = gen.params
+    # text encoders on the HOST (pinned) so the e2e arm pays the H2D copy of their outputs
     host_t5 = sampling.SyntheticEmbedder(pm.context_in_dim, gen.t5.max_length, "cpu")
     host_clip = sampling.SyntheticEmbedder(pm.vec_in_dim, None, "cpu")
-    for e, texts in ((host_t5, [prompt] + concepts), (host_clip, [prompt, " ".join(concepts)])):
+    for e, texts in ((host_t5, [prompt, ""] + concepts), (host_clip, [prompt, "", " ".join(concepts)])):
         for t in texts:
             e(t)
         e._cache = {k: v.pin_memory() for k, v in e._cache.items()}
-    host_lat = [torch.randn(1, 16, side // 8, side // 8, generator=torch.Generator().manual_seed(1000 * rank + i))
+    seed0 = 0 if sharded else 1000 * rank
+    host_lat = [torch.randn(batch, 16, side // 8, side // 8, generator=torch.Generator().manual_seed(seed0 + i))
                 .to(torch.bfloat16).pin_memory() for i in range(args.steps + args.warmup)]
     dev_lat = [l.to(dev) for l in host_lat]
     P, T, H = (side // 16) ** 2, gen.t5.max_length, pm.num_heads
@@ -130,12 +158,19 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     # ---- arm 1: inputs resident in HBM ------------------------------------------------
-    inps = [gen.prepare_inputs(prompt, concepts, l) for l in dev_lat]
+    if mode == "generate":
+        inps = [gen.prepare_inputs(prompt, concepts, l) for l in dev_lat]
 
-    def device_step(i):
-        acc = HeatmapAccumulator(1, C, P, dev, layers, list(range(nsteps)), True, "sparsemax")
-        gen.denoise(inps[i], sched, 0.0, acc)
-        return acc.finalize()
+        def device_step(i):
+            acc = HeatmapAccumulator(1, C, P, dev, layers, list(range(nsteps)), True, "sparsemax",
+                                     per_pair=bool(wl.get("per_pair")))
+            gen.denoise(inps[i], sched, guidance, acc)
+            return acc.finalize()
+    else:
+        def device_step(i):
+            out = pipe.encode_image(dev_lat[i], concepts, prompt="", width=side, height=side,
+                                    layer_indices=layers, num_steps=nsteps, return_device_tensors=True)
+            return out.concept_heatmaps, out.cross_attention_maps
 
     for i in range(args.warmup):
         device_step(i)
@@ -157,29 +192,45 @@ def run_ours(args, rank, world, local_rank):
     launches = ops.LAUNCHES
     attn_ms = sum(ev[0].elapsed_time(ev[1]) for ev, *_ in ops.ATTN_EVENTS)
     n_attn = len(ops.ATTN_EVENTS)
-    attn_flops = sum(B * attention_flops(Pq, Tq, Cq, H, Cq > 0) for _, B, Pq, Tq, Cq in ops.ATTN_EVENTS)
+    attn_flops = sum(B * attention_flops(Pq, Tq, Cq, Hq, Cq > 0) for _, B, Pq, Tq, Cq, Hq in ops.ATTN_EVENTS)
     ops.ATTN_EVENTS = None
 
     # ---- arm 2: end to end through the public API with host buffers ---------------------
     gen.t5, gen.clip = host_t5, host_clip
 
     def e2e_step(i):
-        return pipe.generate_image(prompt, concepts, width=side, height=side, layer_indices=layers,
-                                   return_pil_heatmaps=False, num_inference_steps=nsteps,
-                                   latents=host_lat[i], decode_image=False)
-    for i in range(args.warmup):
-        e2e_step(i)
+        if mode == "generate":
+            o = pipe.generate_image(prompt, concepts, width=side, height=side, layer_indices=layers,
+                                    return_pil_heatmaps=False, num_inference_steps=nsteps,
+                                    guidance=guidance, latents=host_lat[i], decode_image=False)
+        else:
+            o = pipe.encode_image(host_lat[i], concepts, prompt="", width=side, height=side,
+                                  layer_indices=layers, num_steps=nsteps, return_pil_heatmaps=False)
+        return o
+    def gather_maps(outs_):
+        # data parallel: the only communication of the run — gather the per-image maps on rank 0
+        if world == 1 or sharded:
+            return
+        local = torch.as_tensor(np.stack([np.asarray(o.concept_heatmaps).reshape(batch, C, -1)
+                                          for o in outs_])).reshape(len(outs_) * batch, C, -1).to(dev)
+        gather_results(local, len(outs_) * batch * world, rank, world, dst=0)
+
+    gather_maps([e2e_step(i) for i in range(args.warmup)])     # also creates the NCCL communicator
     barrier()
     t0 = time.perf_counter()
     e0.record()
+    outs = []
     for i in range(args.steps):
-        out = e2e_step(args.warmup + i)
+        outs.append(e2e_step(args.warmup + i))
+    out = outs[-1]
+    gather_maps(outs)
     e1.record()
     barrier()
     ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)
-    h2d = (host_lat[0].numel() * 2 + T * pm.context_in_dim * 2 + pm.vec_in_dim * 2 * 2
+    nprompt = 1 if mode == "generate" else batch
+    h2d = (host_lat[0].numel() * 2 + nprompt * (T * pm.context_in_dim * 2 + pm.vec_in_dim * 2) + pm.vec_in_dim * 2
            + C * pm.context_in_dim * 2)
-    d2h = 2 * C * P * 4
+    d2h = 2 * batch * C * P * 4
 
     if world > 1:
         t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
@@ -192,17 +243,23 @@ def run_ours(args, rank, world, local_rank):
     if os.path.exists(tpath):
         with open(tpath) as f:
             traffic = json.load(f).get("dram_bytes_per_launch")
+    images = args.steps * batch * (1 if sharded else world)
+    blocks = "19 double + 38 single blocks" if mode == "generate" else "19 double blocks (stop_after_multimodal_attentions)"
     line = {
-        "metric": METRIC, "value": world * args.steps / (ms_dev * 1e-3), "unit": "images/s",
+        "metric": METRIC, "value": images / (ms_dev * 1e-3), "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        "scaling": "strong" if sharded else "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random-init weights, randn latents/embeddings)",
         "config": {"workload": f"{args.config}: {wl['model']} {side}x{side}, P={P} T={T} C={C}, "
-                               f"{nsteps} denoise steps x (19 double + 38 single blocks), heatmaps from "
+                               f"{mode}: {nsteps if mode == 'generate' else 1} DiT pass(es) x ({blocks}), heatmaps from "
                                f"layers {layers[0]}..{layers[-1]} both spaces",
-                   "images_per_step_per_gpu": 1, "parallelism": f"dp{world} (one image stream per GPU, no collective)",
+                   "images_per_step_per_gpu": batch,
+                   "parallelism": (f"heads sharded {H}/{world} per GPU, all-reduce of partial heatmap logits + "
+                                   f"all-gather of attention outputs (NCCL)") if sharded else
+                                  f"dp{world} (one image stream per GPU, no collective on the data path)",
                    "cache": "inputs larger than L2: 23.8 GB of bf16 weights stream through every step"},
-        "e2e": {"value": world * args.steps / (ms_e2e * 1e-3), "unit": "images/s",
+        "e2e": {"value": images / (ms_e2e * 1e-3), "unit": "images/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
         "clocks": clk,
@@ -241,7 +298,7 @@ def run_reference(args):
     ids = oracle.image_ids(1, side // 16, side // 16)
     pe = oracle.rope_table(torch.cat((torch.zeros(1, T, 3), ids), 1), pm.axes_dim, pm.theta)
     pe_c = oracle.rope_table(torch.cat((torch.zeros(1, C, 3), ids), 1), pm.axes_dim, pm.theta)
-    nl = len(layers)
+    nl = min(len(layers), 4)
 
     def sample():
         t0 = time.perf_counter()
@@ -255,6 +312,8 @@ def run_reference(args):
             cv = vecs[b][None, None].expand(1, nl, *vecs[b].shape)
             oracle.heatmaps_from_vectors(iv, cv, list(range(nl)), [0])
         t3 = time.perf_counter()
+        if wl["mode"] == "encode":            # one pass through the 19 double blocks + heatmaps
+            return pm.depth * (t1 - t0) + (t3 - t2_)
         return nsteps * (pm.depth * (t1 - t0) + pm.depth_single_blocks * (t2_ - t1)) + nsteps * (t3 - t2_)
 
     w0 = time.perf_counter()

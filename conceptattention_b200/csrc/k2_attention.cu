@@ -385,6 +385,26 @@ __device__ __forceinline__ void v1_mma(SmemV1& sm, uint32_t tmem, const UnitV1& 
   mma_commit(&sm.o_done);
 }
 
+// 2^x for x <= 0 on the FMA pipe (Cody-Waite split + degree-3 minimax polynomial, max relative
+// error 1.6e-4 << bf16's 3.9e-3): relieves the MUFU.EX2 unit, which needs exactly as many
+// cycles per tile as the tensor core.  Two elements per call (packed f32x2 math).
+__device__ __forceinline__ void exp2_poly2(uint64_t x2, float& e0, float& e1) {
+  float x0, x1;
+  upk64(x2, x0, x1);
+  x2 = pk64(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+  const uint64_t magic = pk64(12582912.f, 12582912.f), nmagic = pk64(-12582912.f, -12582912.f);
+  const uint64_t j2 = add2(x2, magic);                       // round(x) in the low mantissa bits
+  const uint64_t f2 = fma2(add2(j2, nmagic), pk64(-1.f, -1.f), x2);     // x - round(x) in [-.5,.5]
+  uint64_t p2 = fma2(f2, pk64(0.05360212177f, 0.05360212177f), pk64(0.24237291515f, 0.24237291515f));
+  p2 = fma2(p2, f2, pk64(0.69350236654f, 0.69350236654f));
+  p2 = fma2(p2, f2, pk64(0.99994814396f, 0.99994814396f));
+  float j0, j1, p0, p1;
+  upk64(j2, j0, j1); upk64(p2, p0, p1);
+  e0 = __int_as_float(__float_as_int(p0) + (__float_as_int(j0) << 23));
+  e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(j1) << 23));
+}
+
+template <int kPolyEvery>
 __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const UnitV1& u,
                                            const AttnParams& p, int t, int b, int h) {
   const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
@@ -392,61 +412,92 @@ __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const Unit
   const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
   const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
   const float scale = p.scale_log2;
+  const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
   float m_used = -INFINITY, l_sum = 0.f;
+
+  // One 32-column chunk of S at a time (two register buffers, the next tcgen05.ld in flight
+  // while the current chunk is processed): pass 1 finds the row max, pass 2 re-reads S from
+  // TMEM (cheap) and writes P.  Keeps the warpgroup at ~110 live registers instead of holding
+  // the whole 128-wide row, which spilled under the 168-register cap of a 384-thread CTA.
+  auto mask_chunk = [&](uint32_t* r, int c0, int valid) {
+    if (valid < kBN) {                                    // ragged last tile of a key segment
+#pragma unroll
+      for (int i = 0; i < 32; ++i) if (c0 + i >= valid) r[i] = 0xff800000u;   // -inf
+    }
+  };
+  auto max_chunk = [&](const uint32_t* r, float mx) {
+    float m0 = __uint_as_float(r[0]), m1 = __uint_as_float(r[1]);
+#pragma unroll
+    for (int i = 2; i < 32; i += 2) {
+      m0 = fmaxf(m0, __uint_as_float(r[i])); m1 = fmaxf(m1, __uint_as_float(r[i + 1]));
+    }
+    return fmaxf(mx, fmaxf(m0, m1));
+  };
 
 #pragma unroll 1
   for (int j = 0; j < u.n_tiles; ++j) {
     int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
     mbar_wait(&sm.s_full[t], j & 1);
     tc_fence_after();
-    uint32_t sr[kBN];
-#pragma unroll
-    for (int c = 0; c < kBN; c += 32) tmem_ld32(t_s + c, sr + c);
-    tmem_wait_ld();
-    if (valid < kBN) {                                    // ragged last tile of a key segment
-#pragma unroll
-      for (int c = 0; c < kBN; ++c) if (c >= valid) sr[c] = 0xff800000u;   // -inf
-    }
-    float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
-    float mx2 = __uint_as_float(sr[2]), mx3 = __uint_as_float(sr[3]);
-#pragma unroll
-    for (int c = 4; c < kBN; c += 4) {
-      mx0 = fmaxf(mx0, __uint_as_float(sr[c]));     mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
-      mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2])); mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
-    }
-    const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+    uint32_t ra[32], rb[32];
+    // ---- pass 1: row max ---------------------------------------------------------------
+    float mx = -INFINITY;
+    tmem_ld32(t_s, ra);        tmem_wait_ld32(ra);
+    tmem_ld32(t_s + 32, rb);   mask_chunk(ra, 0, valid);  mx = max_chunk(ra, mx);  tmem_wait_ld32(rb);
+    tmem_ld32(t_s + 64, ra);   mask_chunk(rb, 32, valid); mx = max_chunk(rb, mx);  tmem_wait_ld32(ra);
+    tmem_ld32(t_s + 96, rb);   mask_chunk(ra, 64, valid); mx = max_chunk(ra, mx);  tmem_wait_ld32(rb);
+    tmem_ld32(t_s, ra);        mask_chunk(rb, 96, valid); mx = max_chunk(rb, mx);  // chunk 0 again, in flight
+
     const bool grow = (mx - m_used) * scale > kRescaleThreshold;   // true on the first tile
     const float m_new = grow ? mx : m_used;
     if (j > 0 && __any_sync(0xffffffffu, grow)) {
       // PV_t(j-1) has completed: the commit behind s_full[t] covers it.
       const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
       l_sum *= alpha;
+      tmem_wait_ld32(ra);
 #pragma unroll
       for (int c = 0; c < kD; c += 32) {
-        uint32_t r[32];
-        tmem_ld32(t_o + c, r);
-        tmem_wait_ld();
+        tmem_ld32(t_o + c, rb);
+        tmem_wait_ld32(rb);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-        tmem_st32(t_o + c, r);
+        for (int i = 0; i < 32; ++i) rb[i] = __float_as_uint(__uint_as_float(rb[i]) * alpha);
+        tmem_st32(t_o + c, rb);
       }
     }
     m_used = m_new;
     const float mb = m_used * scale;
-    float rs0 = 0.f, rs1 = 0.f;
-#pragma unroll
-    for (int c = 0; c < kBN; c += 32) {
+    const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
+    uint64_t rs2 = pk64(0.f, 0.f);
+    // ---- pass 2: P = exp2(S*scale - m), bf16, written over S columns [0,64) ----------------
+    auto exp_chunk = [&](uint32_t* r, int c0) {
+      mask_chunk(r, c0, valid);
       uint32_t pk[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
-        const float e0 = ex2(fmaf(__uint_as_float(sr[c + 2 * i]), scale, -mb));
-        const float e1 = ex2(fmaf(__uint_as_float(sr[c + 2 * i + 1]), scale, -mb));
-        rs0 += e0; rs1 += e1;
+        const uint64_t x2 = fma2(pk64(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), scale2, nmb2);
+        float e0, e1;
+        if (kPolyEvery > 0 && (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1) {
+          exp2_poly2(x2, e0, e1);
+        } else {
+          float x0, x1;
+          upk64(x2, x0, x1);
+          e0 = ex2(x0); e1 = ex2(x1);
+        }
+        rs2 = add2(rs2, pk64(e0, e1));
         pk[i] = pack2(e0, e1);
       }
-      tmem_st16(t_s + (c >> 1), pk);                     // P_t over the first 64 columns of S_t
+      tmem_st16(t_s + (c0 >> 1), pk);
+    };
+    tmem_wait_ld32(ra);
+    tmem_ld32(t_s + 32, rb);   exp_chunk(ra, 0);    tmem_wait_ld32(rb);
+    tmem_ld32(t_s + 64, ra);   exp_chunk(rb, 32);   tmem_wait_ld32(ra);
+    tmem_ld32(t_s + 96, rb);   exp_chunk(ra, 64);   tmem_wait_ld32(rb);
+    exp_chunk(rb, 96);
+    {
+      float r0, r1;
+      upk64(rs2, r0, r1);
+      l_sum += r0 + r1;
     }
-    l_sum += rs0 + rs1;
     tmem_wait_st();
     tc_fence_before();
     __syncwarp();
@@ -462,15 +513,16 @@ __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const Unit
     uint32_t r[32];
     tmem_ld32(t_o + c, r);
     tmem_wait_ld();
-    if (row < u.q_rows[t]) {
+    if (row < q_rows) {
       float o[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
-      store_out_row(p, b, h, u.q_row0[t] + row, o, inv_l, c, 32);
+      store_out_row(p, b, h, q_row0 + row, o, inv_l, c, 32);
     }
   }
 }
 
+template <int kPolyEvery>
 __global__ void __launch_bounds__(384, 1)
 attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
@@ -495,16 +547,16 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   const uint32_t tmem = sm.tmem_base;
 
   if (warp < 4) {
-    setmaxnreg_dec<40>();
+    setmaxnreg_dec<96>();
     if (warp == 0) {
       if (elect_one()) v1_producer(sm, &tmq, &tmk, &tmv, u, bh);
     } else if (warp == 1) {
       if (elect_one()) v1_mma(sm, tmem, u);
     }
   } else {
-    setmaxnreg_inc<232>();
+    setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
-    if (t < u.n_q) v1_softmax(sm, tmem, u, p, t, b, h);
+    if (t < u.n_q) v1_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
   }
   tc_fence_before();
   __syncthreads();
@@ -591,8 +643,11 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
     const int units = (p.n_main_tiles + 1) / 2 + (concept_attn ? 1 : 0);
     if (units > 0) {
       const int smem = (int)sizeof(SmemV1) + 1024;
-      CA_CUDA_OK(cudaFuncSetAttribute(attn_v1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      attn_v1_kernel<<<dim3(units, B * H), 384, smem, st>>>(tmq, tmk, tmv, p);
+      // impl 0: polynomial exp2 on every 4th element pair; 2: all MUFU; 3: every 2nd pair
+      auto kern = g_attention_impl == 2 ? attn_v1_kernel<0>
+                : g_attention_impl == 3 ? attn_v1_kernel<2> : attn_v1_kernel<4>;
+      CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      kern<<<dim3(units, B * H), 384, smem, st>>>(tmq, tmk, tmv, p);
       CA_LAUNCH_CHECK();
     }
   }

@@ -168,6 +168,12 @@ class FluxDiTEngine:
             w = self.sd.pop(f"single_blocks.{i}.linear2.weight")
             self.sd[f"single_blocks.{i}.linear2a.weight"] = w[:, :D].contiguous()
             self.sd[f"single_blocks.{i}.linear2b.weight"] = w[:, D:].contiguous()
+            # linear1 = [qkv | mlp] rows: two GEMMs so the mlp half can carry the GELU epilogue
+            w1, b1 = self.sd.pop(f"single_blocks.{i}.linear1.weight"), self.sd.pop(f"single_blocks.{i}.linear1.bias")
+            self.sd[f"single_blocks.{i}.linear1q.weight"] = w1[:3 * D].contiguous()
+            self.sd[f"single_blocks.{i}.linear1q.bias"] = b1[:3 * D].contiguous()
+            self.sd[f"single_blocks.{i}.linear1m.weight"] = w1[3 * D:].contiguous()
+            self.sd[f"single_blocks.{i}.linear1m.bias"] = b1[3 * D:].contiguous()
         if self.hs is not None and self.hs.world > 1:
             rows = self.hs.qkv_rows(128).to(self.device)
             for i in range(params.depth):
@@ -181,6 +187,12 @@ class FluxDiTEngine:
     # -- helpers ---------------------------------------------------------------------
     def _lin(self, prefix, x):
         return F.linear(x, self.sd[prefix + ".weight"], self.sd.get(prefix + ".bias"))
+
+    def _lin_gelu(self, prefix, x):
+        """gelu_tanh(x W^T + b) with the activation in the cuBLASLt epilogue (library GEMM)."""
+        w, b = self.sd[prefix + ".weight"], self.sd[prefix + ".bias"]
+        y = torch._addmm_activation(b, x.reshape(-1, x.shape[-1]), w.t(), use_gelu=True)
+        return y.view(*x.shape[:-1], w.shape[0])
 
     def _mlp_embed(self, prefix, x):
         return self._lin(prefix + ".out_layer", F.silu(self._lin(prefix + ".in_layer", x)))
@@ -279,7 +291,7 @@ class FluxDiTEngine:
                                               (txtc, attn_tc, txt_mod, con_mod, T, "txt")):
                 proj = self._lin(f"{pre}.{s}_attn.proj", attn)
                 h = ops.gate_residual_ln_modulate(x, proj, m0, m1, split, 2 * D, 3 * D, 4 * D)
-                h = self._lin(f"{pre}.{s}_mlp.2", F.gelu(self._lin(f"{pre}.{s}_mlp.0", h), approximate="tanh"))
+                h = self._lin(f"{pre}.{s}_mlp.2", self._lin_gelu(f"{pre}.{s}_mlp.0", h))
                 ops.gate_residual_ln_modulate(x, h, m0, m1, split, 5 * D, 0, 0, want_out=False)
         if collect_vectors:
             collected = {k: torch.stack(v, 0) for k, v in collected.items()}
@@ -296,7 +308,9 @@ class FluxDiTEngine:
         for i in range(p.depth_single_blocks):
             pre = f"single_blocks.{i}"
             mod = self._lin(pre + ".modulation.lin", svec[:B])                    # [B,3D]
-            h = self._lin(pre + ".linear1", ops.ln_modulate(x, mod, None, None, 0, D))   # [B,N,3D+M]
+            xm = ops.ln_modulate(x, mod, None, None, 0, D)
+            h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3D]
+            g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M] gelu in epilogue
             q, k, v = ops.qkv_prep(h, None, (self.sd[pre + ".norm.query_norm.scale"],
                                              self.sd[pre + ".norm.key_norm.scale"]), None, rope_s, H)
             if B == 1:
@@ -305,8 +319,7 @@ class FluxDiTEngine:
             else:
                 attn = torch.cat(ops.joint_attention(q, k, v, P, T, 0), 1)
             out = F.linear(attn, self.sd[pre + ".linear2a.weight"], self.sd[pre + ".linear2.bias"])
-            out = out.view(-1, D).addmm_(F.gelu(h[..., 3 * D:], approximate="tanh").reshape(-1, M),
-                                         self.sd[pre + ".linear2b.weight"].t()).view(B, N, D)
+            out = out.view(-1, D).addmm_(g.view(-1, M), self.sd[pre + ".linear2b.weight"].t()).view(B, N, D)
             ops.gate_residual_ln_modulate(x, out, mod, None, None, 2 * D, 0, 0, want_out=False)
         x = x[:, :P].contiguous()
         ada = self._lin("final_layer.adaLN_modulation.1", svec[:B])               # [B,2D] shift|scale

@@ -125,7 +125,7 @@ def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_tx
         _stream(q)), "ca_joint_attention")
     if ev is not None:
         ev[1].record()
-        ATTN_EVENTS.append((ev, B, P, T, C))
+        ATTN_EVENTS.append((ev, B, P, T, C, H))
     return out_img, out_txtc
 
 
