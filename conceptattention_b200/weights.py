@@ -43,12 +43,15 @@ CONFIGS = {
     # the golden fixtures and the fast tests.
     "tiny": FluxParams(in_channels=64, vec_in_dim=32, context_in_dim=64, hidden_size=256,
                        num_heads=2, depth=3, depth_single_blocks=2, guidance_embed=False),
+    # full Flux width (D=3072, 24 heads) but 2 double + 1 single block: BASELINE config 1 shapes at a
+    # depth the fp32 CPU oracle finishes in seconds (full-dimension parity test)
+    "schnell-2l": FluxParams(depth=2, depth_single_blocks=1, guidance_embed=False),
     "tiny-dev": FluxParams(in_channels=64, vec_in_dim=32, context_in_dim=64, hidden_size=256,
                            num_heads=2, depth=2, depth_single_blocks=1, guidance_embed=True),
 }
 
 # T5 sequence length per model (concept_attention/image_generator.py:57)
-T5_MAX_LENGTH = {"flux-schnell": 256, "flux-dev": 512, "tiny": 128, "tiny-dev": 128}
+T5_MAX_LENGTH = {"flux-schnell": 256, "flux-dev": 512, "tiny": 128, "tiny-dev": 128, "schnell-2l": 256}
 
 
 def linear_shapes(p: FluxParams) -> dict:

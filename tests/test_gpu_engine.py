@@ -157,6 +157,40 @@ def test_accumulated_heatmaps_match_oracle(concept_scale):
     assert (bm == oracle.binary_masks(out.float().cpu())).float().mean() >= 0.995
 
 
+def test_full_width_blocks_match_oracle():
+    """BASELINE config 1 shapes (Flux-schnell width: D=3072, 24 heads, 256x256 -> P=256, T=256,
+    4 concepts, 1 step) through 2 double + 1 single block: engine (bf16, CUDA) vs the fp32 CPU
+    oracle, bounded by the bf16 floor of the reference op sequence; heatmap kernels vs the oracle
+    on the same vectors at the north_star tolerance."""
+    from conceptattention_b200.dit import FluxDiTEngine, HeatmapAccumulator
+    p = CONFIGS["schnell-2l"]
+    sd = init_state_dict(p, seed=3)
+    eng = FluxDiTEngine(p, sd, device="cuda:0")
+    inp = gi.dit_inputs(p, 256, 256, 4, seed=5)
+    t, gd = torch.full((1,), 1.0), torch.zeros(1)
+    sd32 = {k: v.to(BF16).float() for k, v in sd.items()}
+    ii = {k: v.to(BF16).float() for k, v in inp.items()}
+    pred32, vec32 = oracle.dit_forward(sd32, p.asdict(), ii["img"], ii["img_ids"], ii["txt"], ii["txt_ids"],
+                                       ii["concepts"], ii["concept_ids"], ii["concept_vec"], t, ii["vec"], None)
+    golden = lambda k: pred32 if k == "pred" else vec32[k]
+    floor = _bf16_floor(p, sd, inp, t, gd, golden)
+    acc = HeatmapAccumulator(1, 4, 256, "cuda:0", [0, 1], None)
+    pred, vecs = eng(img=inp["img"], img_ids=inp["img_ids"], txt=inp["txt"], txt_ids=inp["txt_ids"],
+                     concepts=inp["concepts"], concept_ids=inp["concept_ids"],
+                     concept_vec=inp["concept_vec"], y=inp["vec"], timesteps=t, accumulator=acc)
+    for k in oracle.VECTOR_KEYS:
+        r = _rel(vecs[k], vec32[k])
+        print(f"full width {k}: engine {r:.3e} floor {floor[k]:.3e}")
+        assert r <= max(2e-2, 1.5 * floor[k]), (k, r, floor[k])
+    assert _rel(pred, pred32) <= max(2e-2, 1.5 * floor["pred"])
+    out, cross = acc.finalize()
+    for got, (a, b) in zip((out, cross), (("output_space_image_vectors", "output_space_concept_vectors"),
+                                         ("cross_attention_image_vectors", "cross_attention_concept_vectors"))):
+        same = oracle.heatmaps_from_vectors(vecs[a][None].float().cpu(), vecs[b][None].float().cpu(), [0, 1], [0])
+        assert _rel_map(got, same) < 1e-2
+        assert (got.float().cpu().argmax(1) == same.argmax(1)).float().mean().item() >= 0.999
+
+
 def test_pipeline_api_generate_and_encode():
     """Public API smoke: same call shapes / error behaviour as the reference class."""
     from conceptattention_b200 import ConceptAttentionFluxPipeline, ConceptAttentionPipelineOutput
