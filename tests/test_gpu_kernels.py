@@ -170,3 +170,50 @@ def test_joint_attention_full_size_properties(ops, P, T, C, H):
     for j, h in enumerate(hs):
         close(oi[..., h * 128:(h + 1) * 128], ri[..., j * 128:(j + 1) * 128], rtol=2e-2, atol=5e-3)
         close(ot[..., h * 128:(h + 1) * 128], rt[..., j * 128:(j + 1) * 128], rtol=2e-2, atol=5e-3)
+
+
+# ---------------------------------------------------------------- C-ABI error behaviour / edges
+def test_cabi_status_codes_and_empty_inputs(ops):
+    """Error convention of include/conceptattention_b200.h: int status, never throws; empty
+    problems are no-ops; shapes outside the kernels' range are refused, not mis-computed."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    q = torch.zeros(1, 2, 40, 128, device="cuda", dtype=BF16)
+    oi = torch.zeros(1, 32, 256, device="cuda", dtype=BF16)
+    ot = torch.zeros(1, 8, 256, device="cuda", dtype=BF16)
+    ptr = lambda t: t.data_ptr()
+    call = lambda *a: lib.ca_joint_attention(*a, None)
+    assert call(ptr(q), ptr(q), ptr(q), 1, 2, 32, 4, 4, 0, ptr(oi), ptr(ot)) == 0
+    assert call(None, ptr(q), ptr(q), 1, 2, 32, 4, 4, 0, ptr(oi), ptr(ot)) == -1          # null pointer
+    assert call(ptr(q), ptr(q), ptr(q), 1, 2, 32, 4, 4, 7, ptr(oi), ptr(ot)) == -1        # bad mode
+    assert call(ptr(q), ptr(q), ptr(q), 1, 2, 32, 4, 33, 0, ptr(oi), ptr(ot)) == -2       # C > 32
+    assert call(ptr(q) + 2, ptr(q), ptr(q), 1, 2, 32, 4, 4, 0, ptr(oi), ptr(ot)) == -3    # misaligned
+    assert call(ptr(q), ptr(q), ptr(q), 0, 2, 32, 4, 4, 0, ptr(oi), ptr(ot)) == 0         # empty batch
+    assert lib.ca_device_check(0) == 0
+    acc = torch.zeros(1, 4, 32, device="cuda")
+    st = lambda *a: lib.ca_heatmap_accumulate(*a, None)
+    assert st(ptr(oi), 32 * 256, 0, 256, ptr(ot), 8 * 256, 0, 256, 1, 256, 1, 32, 4, 0, 0, ptr(acc)) == 0
+    assert st(ptr(oi), 32 * 256, 0, 256, ptr(ot), 8 * 256, 0, 256, 1, 256, 1, 32, 4, 9, 0, ptr(acc)) == -1   # bad norm
+    assert st(ptr(oi), 32 * 256, 0, 256, ptr(ot), 8 * 256, 0, 256, 1, 256, 1, 32, 40, 0, 0, ptr(acc)) == -2  # C > 32
+    assert st(ptr(oi), 32 * 256, 0, 250, ptr(ot), 8 * 256, 0, 256, 1, 256, 1, 32, 4, 0, 0, ptr(acc)) == -3   # stride % 8
+    assert st(ptr(oi), 32 * 256, 0, 256, ptr(ot), 8 * 256, 0, 256, 1, 256, 1, 0, 4, 0, 0, ptr(acc)) == 0     # P = 0
+    assert lib.ca_argmax_mask(None, None, 1, 2, 4, 0, None) == -1
+    assert lib.ca_status_string(-2).decode() == "unsupported shape"
+    torch.cuda.synchronize()
+    assert float(acc.abs().sum()) > 0      # the valid call did accumulate (softmax rows sum to 1)
+    torch.testing.assert_close(acc.sum(1).cpu(), torch.ones(1, 32))
+
+
+def test_joint_attention_max_concepts_and_single_concept(ops):
+    """C = 32 (CA_MAX_CONCEPTS) and C = 1 through the concept tile; ragged P and T."""
+    for C in (1, 32):
+        B, H, P, T = 1, 2, 200, 77
+        q, k, v = (rnd(B, H, P + T + C, 128, seed=40 + i, scale=0.6) for i in range(3))
+        oi, ot = ops.joint_attention(q.cuda(), k.cuda(), v.cuda(), P, T, C)
+        qf, kf, vf = q.float(), k.float(), v.float()
+        main = oracle.sdpa(qf[:, :, :P + T], kf[:, :, :P + T], vf[:, :, :P + T])
+        idx = list(range(P)) + list(range(P + T, P + T + C))
+        con = oracle.sdpa(qf[:, :, P + T:], kf[:, :, idx], vf[:, :, idx])
+        close(oi, oracle.merge_heads(main[:, :, :P]), rtol=2e-2, atol=2e-2)
+        close(ot[:, :T], oracle.merge_heads(main[:, :, P:]), rtol=2e-2, atol=2e-2)
+        close(ot[:, T:], oracle.merge_heads(con), rtol=2e-2, atol=2e-2)
