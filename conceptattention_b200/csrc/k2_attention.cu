@@ -276,6 +276,7 @@ struct SmemV1 {
   uint8_t kv[kKvStages][kTileBytes];
   uint64_t q_full[2], kv_full[kKvStages], kv_empty[kKvStages], s_full[2], p_full[2], o_done;
   uint32_t tmem_base;
+  float xchg[2][2][kBM];        // v3: row max / row sum exchange between the two column halves
 };
 
 struct UnitV1 {
@@ -522,7 +523,150 @@ __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const Unit
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// v3 softmax: BOTH softmax warpgroups work on the SAME tile, split by key columns (warpgroup
+// `half` owns S columns [64*half, 64*half+64)), then move to the other tile together.
+// Why: MUFU.EX2 is quarter rate — a warp that has just issued one cannot issue its next MUFU
+// for 8 cycles, and ptxas clusters the MUFUs of a chunk, so a lone warp per SM sub-partition
+// (v1/v2: one warpgroup per tile, the two alternating) idles through those slots (ncu: 592
+// instructions took ~2000 cycles).  With two warps of the same tile co-resident on each
+// sub-partition one warp's FMA/pack work fills the other's MUFU shadow.
+// The two threads that share a row exchange their partial row max through shared memory
+// (named barrier, 256 threads); that barrier also orders every S read of the tile before
+// any P write, which matters because P (columns [0,64)) overlays the columns warpgroup 0 reads.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void softmax_bar_sync() {
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+}
+
 template <int kPolyEvery>
+__device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const UnitV1& u,
+                                           const AttnParams& p, int half, int b, int h) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const float scale = p.scale_log2;
+  const int c0 = half * 64;
+  float m_used[2] = {-INFINITY, -INFINITY}, l_sum[2] = {0.f, 0.f};
+  uint32_t use = 0;                                       // exchange-buffer parity
+
+  auto mask_chunk = [&](uint32_t* r, int cbase, int valid) {
+    if (valid < kBN) {                                    // ragged last tile of a key segment
+#pragma unroll
+      for (int i = 0; i < 32; ++i) if (cbase + i >= valid) r[i] = 0xff800000u;   // -inf
+    }
+  };
+  auto max_chunk = [&](const uint32_t* r, float mx) {
+    float m0 = __uint_as_float(r[0]), m1 = __uint_as_float(r[1]);
+#pragma unroll
+    for (int i = 2; i < 32; i += 2) {
+      m0 = fmaxf(m0, __uint_as_float(r[i])); m1 = fmaxf(m1, __uint_as_float(r[i + 1]));
+    }
+    return fmaxf(mx, fmaxf(m0, m1));
+  };
+  auto exchange = [&](float mine, bool take_max) {        // combine with the row's other thread
+    float* xb = &sm.xchg[use & 1][0][0];
+    xb[half * kBM + row] = mine;
+    softmax_bar_sync();
+    const float other = xb[(half ^ 1) * kBM + row];
+    ++use;
+    return take_max ? fmaxf(mine, other) : mine + other;
+  };
+
+#pragma unroll 1
+  for (int j = 0; j < u.n_tiles; ++j) {
+    int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      if (t < u.n_q) {
+        const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
+        mbar_wait(&sm.s_full[t], j & 1);
+        tc_fence_after();
+        uint32_t ra[32], rb[32];
+        tmem_ld32(t_s + c0, ra);
+        tmem_ld32(t_s + c0 + 32, rb);
+        tmem_wait_ld32(ra);
+        tmem_wait_ld32(rb);
+        mask_chunk(ra, c0, valid);
+        mask_chunk(rb, c0 + 32, valid);
+        const float mx = exchange(max_chunk(rb, max_chunk(ra, -INFINITY)), true);
+        const bool grow = (mx - m_used[t]) * scale > kRescaleThreshold;   // true on the first tile
+        const float m_new = grow ? mx : m_used[t];
+        if (j > 0 && __any_sync(0xffffffffu, grow)) {
+          // PV_t(j-1) has completed: the commit behind s_full[t] covers it.
+          const float alpha = grow ? ex2((m_used[t] - m_new) * scale) : 1.f;
+          l_sum[t] *= alpha;
+#pragma unroll
+          for (int c = 0; c < 64; c += 32) {
+            uint32_t rc[32];
+            tmem_ld32(t_o + c0 + c, rc);
+            tmem_wait_ld32(rc);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+            tmem_st32(t_o + c0 + c, rc);
+          }
+        }
+        m_used[t] = m_new;
+        const float mb = m_new * scale;
+        const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
+        uint64_t rs2 = pk64(0.f, 0.f);
+        auto exp_chunk = [&](const uint32_t* r, int pcol) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const uint64_t x2 = fma2(pk64(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), scale2, nmb2);
+            float e0, e1;
+            if (kPolyEvery > 0 && (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1) {
+              exp2_poly2(x2, e0, e1);
+            } else {
+              float x0, x1;
+              upk64(x2, x0, x1);
+              e0 = ex2(x0); e1 = ex2(x1);
+            }
+            rs2 = add2(rs2, pk64(e0, e1));
+            pk[i] = pack2(e0, e1);
+          }
+          tmem_st16(t_s + pcol, pk);                      // P_t over S_t columns [0,64)
+        };
+        exp_chunk(ra, half * 32);
+        exp_chunk(rb, half * 32 + 16);
+        float r0, r1;
+        upk64(rs2, r0, r1);
+        l_sum[t] += r0 + r1;
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.p_full[t]);
+      }
+    }
+  }
+
+  // ---- epilogue: O_t / l -> bf16 "B L (H D)"; this thread owns columns [c0, c0+64) -------
+  mbar_wait(&sm.o_done, 0);
+  tc_fence_after();
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    if (t < u.n_q) {
+      const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
+      const float inv_l = 1.f / exchange(l_sum[t], false);
+      const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+#pragma unroll
+      for (int c = 0; c < 64; c += 32) {
+        uint32_t r[32];
+        tmem_ld32(t_o + c0 + c, r);
+        tmem_wait_ld32(r);
+        if (row < q_rows) {
+          float o[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+          store_out_row(p, b, h, q_row0 + row, o, inv_l, c0 + c, 32);
+        }
+      }
+    }
+  }
+}
+
+template <int kPolyEvery, bool kCoop>
 __global__ void __launch_bounds__(384, 1)
 attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
@@ -536,7 +680,7 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
     prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
     mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
     for (int i = 0; i < kKvStages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], kCoop ? 8 : 4); }
     mbar_init(&sm.o_done, 1);
     fence_barrier_init();
   }
@@ -556,7 +700,8 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   } else {
     setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
-    if (t < u.n_q) v1_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+    if (kCoop) v3_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+    else if (t < u.n_q) v1_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
   }
   tc_fence_before();
   __syncthreads();
@@ -643,9 +788,12 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
     const int units = (p.n_main_tiles + 1) / 2 + (concept_attn ? 1 : 0);
     if (units > 0) {
       const int smem = (int)sizeof(SmemV1) + 1024;
-      // impl 0: polynomial exp2 on every 4th element pair; 2: all MUFU; 3: every 2nd pair
-      auto kern = g_attention_impl == 2 ? attn_v1_kernel<0>
-                : g_attention_impl == 3 ? attn_v1_kernel<2> : attn_v1_kernel<4>;
+      // impl 0: v3 (cooperating warpgroups), polynomial exp2 on every 4th element pair;
+      // 4 / 5: v3 with every 2nd pair / all MUFU; 2 / 3: v2 (one warpgroup per tile) all MUFU / every 4th
+      auto kern = g_attention_impl == 2 ? attn_v1_kernel<0, false>
+                : g_attention_impl == 3 ? attn_v1_kernel<4, false>
+                : g_attention_impl == 4 ? attn_v1_kernel<2, true>
+                : g_attention_impl == 5 ? attn_v1_kernel<0, true> : attn_v1_kernel<4, true>;
       CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       kern<<<dim3(units, B * H), 384, smem, st>>>(tmq, tmk, tmv, p);
       CA_LAUNCH_CHECK();
