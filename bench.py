@@ -162,8 +162,11 @@ def run_ours(args, rank, world, local_rank):
         inps = [gen.prepare_inputs(prompt, concepts, l) for l in dev_lat]
 
         def device_step(i):
-            acc = HeatmapAccumulator(1, C, P, dev, layers, list(range(nsteps)), True, "sparsemax",
-                                     per_pair=bool(wl.get("per_pair")))
+            if wl.get("per_pair"):
+                acc = HeatmapAccumulator(1, C, P, dev, layers, list(range(nsteps)), True, "sparsemax",
+                                         per_pair=True)
+            else:
+                acc = gen.accumulator(1, C, P, layers, list(range(nsteps)), True, "sparsemax", False)
             gen.denoise(inps[i], sched, guidance, acc)
             return acc.finalize()
     else:
@@ -172,11 +175,11 @@ def run_ours(args, rank, world, local_rank):
                                     layer_indices=layers, num_steps=nsteps, return_device_tensors=True)
             return out.concept_heatmaps, out.cross_attention_maps
 
+    gen.model.use_graphs = not args.no_graphs
     for i in range(args.warmup):
         device_step(i)
     barrier()
     ops.LAUNCHES = 0
-    ops.ATTN_EVENTS = []
     clocks = ClockSampler(local_rank)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -188,12 +191,24 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     torch.cuda.profiler.stop()
     ms_dev = e0.elapsed_time(e1)
-    clk = clocks.stop()
     launches = ops.LAUNCHES
+    # roofline pass: the SAME K steps launch by launch, a CUDA-event pair around every K2 launch
+    # on its stream (events recorded inside a captured graph cannot be read back, so the engine
+    # does not replay graphs while ATTN_EVENTS is set).
+    ops.ATTN_EVENTS = []
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for i in range(args.steps):
+        device_step(args.warmup + i)
+    e3.record()
+    barrier()
+    ms_eager = e2.elapsed_time(e3)
+    clk = clocks.stop()
     attn_ms = sum(ev[0].elapsed_time(ev[1]) for ev, *_ in ops.ATTN_EVENTS)
     n_attn = len(ops.ATTN_EVENTS)
     attn_flops = sum(B * attention_flops(Pq, Tq, Cq, Hq, Cq > 0) for _, B, Pq, Tq, Cq, Hq in ops.ATTN_EVENTS)
     ops.ATTN_EVENTS = None
+    graphed = gen.model.use_graphs and len(gen.model._graphs) > 0
 
     # ---- arm 2: end to end through the public API with host buffers ---------------------
     gen.t5, gen.clip = host_t5, host_clip
@@ -267,7 +282,11 @@ def run_ours(args, rank, world, local_rank):
                      "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
                      "frac": ach / pk["tflops"], "peak_source": pk["source"], "traffic": traffic,
                      "launches_timed": n_attn, "avg_launch_ms": attn_ms / max(n_attn, 1),
-                     "share_of_step": attn_ms / ms_dev},
+                     "share_of_step": attn_ms / ms_eager,
+                     "timed_in": "launch-by-launch pass of the same K steps run right after the timed "
+                                 "region (CUDA events around each K2 launch on its stream)",
+                     "ms_per_step_launch_by_launch": ms_eager / args.steps},
+        "cuda_graphs": graphed,
     }
     return line, out
 
@@ -346,6 +365,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="schnell-1024", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graphs", action="store_true", help="launch every kernel individually (A/B)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -18,6 +18,7 @@ contract and state-dict keys, re-planned for one B200:
 """
 from __future__ import annotations
 
+import hashlib
 import math
 
 import torch
@@ -56,7 +57,7 @@ class HeatmapAccumulator:
     """
 
     def __init__(self, B, C, P, device, layer_indices, timesteps=None, softmax=True,
-                 attention_norm="sparsemax", round_bf16=False, per_pair=False):
+                 attention_norm="sparsemax", round_bf16=False, per_pair=False, buffer=None):
         if not (softmax or attention_norm in ("softmax", "entmax15", "sparsemax")):
             raise ValueError(f"Unknown attention_norm={attention_norm}")
         self.norm = "softmax" if (softmax or attention_norm == "softmax") else attention_norm
@@ -64,7 +65,11 @@ class HeatmapAccumulator:
         self.timesteps = None if timesteps is None else [int(t) for t in timesteps]
         self.round_bf16 = round_bf16
         self.B, self.C, self.P = B, C, P
-        self.acc = torch.zeros(2, B, C, P, device=device, dtype=torch.float32)
+        if buffer is None:
+            self.acc = torch.zeros(2, B, C, P, device=device, dtype=torch.float32)
+        else:          # caller-owned state (stable address: lets a captured step be replayed)
+            assert buffer.shape == (2, B, C, P) and buffer.dtype == torch.float32
+            self.acc = buffer.zero_()
         self.count = 0
         self.step = 0
         self.per_pair = {} if per_pair else None      # (t, l) -> [2,B,C,P]
@@ -91,6 +96,15 @@ class HeatmapAccumulator:
             ops.heatmap_accumulate(q_pre[:, :, :P], q_pre[:, :, P + T:], acc[1], self.norm,
                                    self.round_bf16, per_head=True)
         self.count += m
+
+    def signature(self, depth):
+        """What a captured forward bakes in for this accumulator at the current step."""
+        return (self.acc.data_ptr(), self.norm, self.round_bf16,
+                tuple(self.multiplicity(i) for i in range(depth)))
+
+    def note_replay(self, depth):
+        """Host bookkeeping of one replayed forward (the kernels ran inside the graph)."""
+        self.count += sum(self.multiplicity(i) for i in range(depth))
 
     def add_logits(self, layer, logits):
         """Head-sharded form: `logits` fp32 [2,B,C,P] (output space, cross space) are the
@@ -174,6 +188,22 @@ class FluxDiTEngine:
             self.sd[f"single_blocks.{i}.linear1q.bias"] = b1[:3 * D].contiguous()
             self.sd[f"single_blocks.{i}.linear1m.weight"] = w1[3 * D:].contiguous()
             self.sd[f"single_blocks.{i}.linear1m.bias"] = b1[3 * D:].contiguous()
+        # every modulation vector of a forward depends only on (vec, concept_vec): ONE
+        # [2B,D]x[D,Mtot] GEMM per forward instead of 3 per double + 1 per single block
+        # (layers.py:113-126 applied 96 times).  The originals become views of the stack.
+        names = [f"double_blocks.{i}.{s}_mod.lin" for i in range(params.depth) for s in ("img", "txt")]
+        names += [f"single_blocks.{i}.modulation.lin" for i in range(params.depth_single_blocks)]
+        names += ["final_layer.adaLN_modulation.1"]
+        self.mod_off, off = {}, 0
+        for n in names:
+            self.mod_off[n] = (off, self.sd[n + ".weight"].shape[0])
+            off += self.sd[n + ".weight"].shape[0]
+        self.mod_w = torch.empty(off, D, device=self.device, dtype=BF16)
+        self.mod_b = torch.empty(off, device=self.device, dtype=BF16)
+        for n in names:
+            o, m = self.mod_off[n]
+            self.mod_w[o:o + m].copy_(self.sd.pop(n + ".weight"))
+            self.mod_b[o:o + m].copy_(self.sd.pop(n + ".bias"))
         if self.hs is not None and self.hs.world > 1:
             rows = self.hs.qkv_rows(128).to(self.device)
             for i in range(params.depth):
@@ -183,6 +213,11 @@ class FluxDiTEngine:
                         if key in self.sd:
                             self.sd[key] = self.sd[key][rows].contiguous()
         self._rope_cache = {}
+        # CUDA graphs of whole forwards (one per signature), captured the second time a
+        # signature is seen; the first call runs launch by launch and warms cuBLAS.
+        self.use_graphs = True
+        self.max_graphs = 8
+        self._graphs, self._graph_seen, self._graph_pool = {}, {}, None
 
     # -- helpers ---------------------------------------------------------------------
     def _lin(self, prefix, x):
@@ -209,15 +244,85 @@ class FluxDiTEngine:
                 return -1
         key = tuple((t.data_ptr(), tuple(t.shape), ver(t), str(t.device)) for t in parts)
         if self._rope_cache.get("key") != key:
+            # new id tensors: look the table up by CONTENT (one small D2H per new id set) so
+            # equal ids always map to the same table address (captured graphs bake it in)
             ids = torch.cat([t.to(self.device, torch.float32) for t in parts], 0)
+            digest = hashlib.sha1(ids.cpu().numpy().tobytes()).hexdigest() + str(tuple(ids.shape))
+            tables = self._rope_cache.setdefault("tables", {})
+            if digest not in tables:
+                if len(tables) >= 16:
+                    tables.pop(next(iter(tables)))
+                tables[digest] = rope_cos_sin(ids, self.p.axes_dim, self.p.theta)
             # keep the id tensors alive so data_ptr cannot be recycled under the key
-            self._rope_cache = {"key": key, "ids": parts,
-                                "table": rope_cos_sin(ids, self.p.axes_dim, self.p.theta)}
+            self._rope_cache.update(key=key, ids=parts, table=tables[digest])
         return self._rope_cache["table"]
 
     # -- forward -----------------------------------------------------------------------
     @torch.no_grad()
     def forward(self, img, img_ids, txt, txt_ids, concepts, concept_ids, concept_vec, timesteps, y,
+                guidance=None, stop_after_multimodal_attentions=False, edit_metadata=None,
+                iteration=None, joint_attention_kwargs=None, accumulator: HeatmapAccumulator = None,
+                collect_vectors=True, **kwargs):
+        """ModifiedFluxDiT.forward contract (see `_forward`).  The fast path
+        (`collect_vectors=False`, one GPU, running accumulator) replays a CUDA graph of the
+        whole forward: ~750 launches per timestep become one cudaGraphLaunch."""
+        args = dict(img=img, txt=txt, concepts=concepts, concept_vec=concept_vec,
+                    timesteps=timesteps, y=y, guidance=guidance)
+        rest = dict(img_ids=img_ids, txt_ids=txt_ids, concept_ids=concept_ids,
+                    stop_after_multimodal_attentions=stop_after_multimodal_attentions,
+                    joint_attention_kwargs=joint_attention_kwargs, accumulator=accumulator,
+                    collect_vectors=collect_vectors)
+        eligible = (self.use_graphs and not collect_vectors and self.hs is None
+                    and ops.ATTN_EVENTS is None
+                    and (accumulator is None or accumulator.per_pair is None)
+                    and concept_vec is not None and img.ndim == 3 and txt.ndim == 3
+                    and not torch.cuda.is_current_stream_capturing())
+        if not eligible:
+            return self._forward(**args, **rest)
+        if self.p.guidance_embed and guidance is None:
+            raise ValueError("Didn't get guidance strength for guidance distilled model.")
+        if not self.p.guidance_embed:
+            args["guidance"] = None
+        rope = self._rope(img_ids, txt_ids, concept_ids)
+        key = (tuple((k, tuple(v.shape)) for k, v in args.items() if v is not None),
+               attention_mode(joint_attention_kwargs), bool(stop_after_multimodal_attentions),
+               rope.data_ptr(), accumulator.signature(self.p.depth) if accumulator is not None else None)
+        ent = self._graphs.get(key)
+        if ent is None:
+            self._graph_seen[key] = self._graph_seen.get(key, 0) + 1
+            if self._graph_seen[key] < 2:
+                return self._forward(**args, **rest)
+            if len(self._graphs) >= self.max_graphs:          # drop the oldest capture
+                self._graphs.pop(next(iter(self._graphs)))
+            ent = self._capture(args, rest, rope)
+            self._graphs[key] = ent
+        elif accumulator is not None:
+            accumulator.note_replay(self.p.depth)
+        for k, v in args.items():
+            if v is not None:
+                ent["static"][k].copy_(v, non_blocking=True)
+        ent["graph"].replay()
+        ops.LAUNCHES += ent["n_launch"]
+        return ent["pred"], {}
+
+    def _capture(self, args, rest, rope):
+        """Capture one forward on static copies of the per-call tensors.  The accumulator's
+        host bookkeeping (count) happens once here, so the caller replays right after."""
+        dev = self.device
+        static = {k: torch.empty(v.shape, device=dev, dtype=BF16) for k, v in args.items() if v is not None}
+        torch.cuda.synchronize(dev)
+        graph = torch.cuda.CUDAGraph()
+        n0 = ops.LAUNCHES
+        if self._graph_pool is None:
+            self._graph_pool = torch.cuda.graph_pool_handle()
+        with torch.cuda.graph(graph, pool=self._graph_pool):
+            pred, _ = self._forward(**{k: static.get(k) for k in args}, **rest)
+        acc = rest["accumulator"]
+        return {"graph": graph, "static": static, "pred": pred, "n_launch": ops.LAUNCHES - n0,
+                "keep": (rope, None if acc is None else acc.acc)}
+
+    @torch.no_grad()
+    def _forward(self, img, img_ids, txt, txt_ids, concepts, concept_ids, concept_vec, timesteps, y,
                 guidance=None, stop_after_multimodal_attentions=False, edit_metadata=None,
                 iteration=None, joint_attention_kwargs=None, accumulator: HeatmapAccumulator = None,
                 collect_vectors=True, **kwargs):
@@ -248,14 +353,19 @@ class FluxDiTEngine:
         txtc = self._lin("txt_in", torch.cat((txt, concepts), 1)).contiguous()   # [B,T+C,D]
         rope = self._rope(img_ids, txt_ids, concept_ids)
         svec = F.silu(torch.cat((vec, cvec), 0))                                  # [2B,D]
+        mods = F.linear(svec, self.mod_w, self.mod_b)                             # [2B,Mtot]
+
+        def mod_of(name, rows):
+            o, m = self.mod_off[name]
+            return mods[rows, o:o + m]
 
         collected = {k: [] for k in VECTOR_KEYS} if collect_vectors else None
         for i in range(p.depth):
             pre = f"double_blocks.{i}"
             sel = collect_vectors or (accumulator is not None and accumulator.multiplicity(i) > 0)
-            img_mod = self._lin(pre + ".img_mod.lin", svec[:B])                   # [B,6D]
-            tc_mod = self._lin(pre + ".txt_mod.lin", svec)                        # [2B,6D]
-            txt_mod, con_mod = tc_mod[:B], tc_mod[B:]
+            img_mod = mod_of(pre + ".img_mod.lin", slice(0, B))                   # [B,6D] views
+            txt_mod = mod_of(pre + ".txt_mod.lin", slice(0, B))
+            con_mod = mod_of(pre + ".txt_mod.lin", slice(B, 2 * B))
             # LN + modulate, qkv GEMMs (concept rows ride on the txt GEMM)
             img_qkv = self._lin(pre + ".img_attn.qkv", ops.ln_modulate(x_img, img_mod, None, None, 0, D))
             tc_qkv = self._lin(pre + ".txt_attn.qkv", ops.ln_modulate(txtc, txt_mod, con_mod, T, 0, D))
@@ -307,7 +417,7 @@ class FluxDiTEngine:
         M = int(D * p.mlp_ratio)
         for i in range(p.depth_single_blocks):
             pre = f"single_blocks.{i}"
-            mod = self._lin(pre + ".modulation.lin", svec[:B])                    # [B,3D]
+            mod = mod_of(pre + ".modulation.lin", slice(0, B))                    # [B,3D] view
             xm = ops.ln_modulate(x, mod, None, None, 0, D)
             h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3D]
             g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M] gelu in epilogue
@@ -322,7 +432,7 @@ class FluxDiTEngine:
             out = out.view(-1, D).addmm_(g.view(-1, M), self.sd[pre + ".linear2b.weight"].t()).view(B, N, D)
             ops.gate_residual_ln_modulate(x, out, mod, None, None, 2 * D, 0, 0, want_out=False)
         x = x[:, :P].contiguous()
-        ada = self._lin("final_layer.adaLN_modulation.1", svec[:B])               # [B,2D] shift|scale
+        ada = mod_of("final_layer.adaLN_modulation.1", slice(0, B))               # [B,2D] shift|scale
         pred = self._lin("final_layer.linear", ops.ln_modulate(x, ada, None, None, 0, D))
         return pred, collected
 

@@ -39,14 +39,23 @@ def _req(t, dtype, name):
     return t
 
 
+def _req_rows(t, dtype, name):
+    """2-D, unit inner stride; rows may be a column slice of a wider matrix."""
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise ValueError(f"{name} must be a CUDA tensor (no CPU path exists)")
+    if t.dtype != dtype or t.ndim != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name} must be a 2-D {dtype} tensor with unit inner stride")
+    return t
+
+
 def ln_modulate(x, mod0, mod1=None, split=None, shift_off=0, scale_off=None, out=None):
     """(1+scale)*LN(x)+shift.  x [B,N,D] bf16; mod0/mod1 [B,M] bf16 rows holding the
     modulation chunks; rows >= split use mod1."""
     B, N, D = x.shape
-    _req(x, BF16, "x"); _req(mod0, BF16, "mod0")
+    _req(x, BF16, "x"); _req_rows(mod0, BF16, "mod0")
     if mod1 is not None:
-        _req(mod1, BF16, "mod1")
-        assert mod1.shape == mod0.shape
+        _req_rows(mod1, BF16, "mod1")
+        assert mod1.shape == mod0.shape and mod1.stride(0) == mod0.stride(0)
     if out is None:
         out = torch.empty_like(x)
     scale_off = D if scale_off is None else scale_off
@@ -62,7 +71,10 @@ def gate_residual_ln_modulate(x, y, mod0, mod1=None, split=None, gate_off=0, shi
     """x += gate*y in place; returns (1+scale)*LN(x)+shift if want_out else None.
     y may be a column slice of a wider matrix (row stride y.stride(-2))."""
     B, N, D = x.shape
-    _req(x, BF16, "x"); _req(mod0, BF16, "mod0")
+    _req(x, BF16, "x"); _req_rows(mod0, BF16, "mod0")
+    if mod1 is not None:
+        _req_rows(mod1, BF16, "mod1")
+        assert mod1.stride(0) == mod0.stride(0)
     assert y.dtype == BF16 and y.is_cuda and y.stride(-1) == 1 and y.shape == x.shape
     assert y.stride(0) == N * y.stride(1) or B == 1
     if want_out and out is None:

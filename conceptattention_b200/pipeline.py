@@ -83,6 +83,19 @@ class FluxGenerator:
                                                    T5_MAX_LENGTH[model_name], self.device)
         self.clip = clip or sampling.SyntheticEmbedder(self.params.vec_in_dim, None, self.device)
         self.ae = ae
+        self._acc_buffers = {}
+
+    def accumulator(self, B, C, P, layer_indices, timesteps, softmax, attention_norm, round_bf16):
+        """HeatmapAccumulator on a generator-owned state buffer: the same address call after
+        call, so the engine's captured forwards stay valid from image to image."""
+        buf = self._acc_buffers.get((B, C, P))
+        if buf is None:
+            if len(self._acc_buffers) >= 4:
+                self._acc_buffers.pop(next(iter(self._acc_buffers)))
+            buf = self._acc_buffers[(B, C, P)] = torch.empty(2, B, C, P, device=self.device,
+                                                              dtype=torch.float32)
+        return HeatmapAccumulator(B, C, P, self.device, layer_indices, timesteps, softmax,
+                                  attention_norm, round_bf16, buffer=buf)
 
     @torch.inference_mode()
     def prepare_inputs(self, prompt, concepts, latents):
@@ -178,8 +191,7 @@ class ConceptAttentionFluxPipeline:
         sched = sampling.get_schedule(num_inference_steps, inp["img"].shape[1],
                                       shift=(not gen.is_schnell))
         B, P, C = inp["img"].shape[0], inp["img"].shape[1], len(concepts)
-        acc = HeatmapAccumulator(B, C, P, dev, layer_indices, timesteps, softmax, attention_norm,
-                                 round_bf16)
+        acc = gen.accumulator(B, C, P, layer_indices, timesteps, softmax, attention_norm, round_bf16)
         x = gen.denoise(inp, sched, guidance, acc, joint_attention_kwargs)
         concept_heatmaps, cross_attention_maps = acc.finalize()
         image = gen.decode(x, height, width) if decode_image else None
@@ -232,8 +244,8 @@ class ConceptAttentionFluxPipeline:
             noised = t * noise + (1.0 - t) * clean
             inp = gen.prepare_inputs(prompt if B == 1 else [prompt] * B, concepts, noised)
             if acc is None:
-                acc = HeatmapAccumulator(B, len(concepts), inp["img"].shape[1], dev, layer_indices,
-                                         None, softmax, attention_norm, round_bf16)
+                acc = gen.accumulator(B, len(concepts), inp["img"].shape[1], layer_indices,
+                                      None, softmax, attention_norm, round_bf16)
             t_vec = torch.full((B,), t, dtype=torch.bfloat16, device=dev)
             g_vec = torch.zeros(B, dtype=torch.bfloat16, device=dev)
             gen.model(img=inp["img"], img_ids=inp["img_ids"], txt=inp["txt"], txt_ids=inp["txt_ids"],

@@ -213,3 +213,43 @@ def test_pipeline_api_generate_and_encode():
     assert enc.concept_heatmaps.shape == (4, 2, 16, 16)
     masks = pipe.segment(torch.as_tensor(enc.concept_heatmaps).cuda(), mode="argmax")
     assert masks.shape == (4, 16, 16) and masks.dtype == torch.int64
+
+
+def test_graph_replay_equals_launch_by_launch():
+    """The captured forward (CUDA graph replay) gives the same heatmaps as launching
+    every kernel individually, across images (new latents, same accumulator buffer) and
+    for a timestep subset (different per-step signatures)."""
+    from conceptattention_b200 import ConceptAttentionFluxPipeline
+    pipe = ConceptAttentionFluxPipeline(model_name="tiny", device="cuda:0")
+    eng = pipe.flux_generator.model
+    kw = dict(width=256, height=256, layer_indices=[1, 2], num_inference_steps=4,
+              return_pil_heatmaps=False, decode_image=False)
+    concepts = ["dragon", "rock", "sky"]
+
+    def run(seed, **extra):
+        o = pipe.generate_image("a dragon on a rock", concepts, seed=seed, **kw, **extra)
+        return np.stack([o.concept_heatmaps, o.cross_attention_maps])
+
+    eng.use_graphs = False
+    ref = [run(s) for s in (0, 1)]
+    ref_sub = run(2, timesteps=[1, 3])
+    eng.use_graphs = True
+    got = [run(s) for s in (0, 1)]           # image 0 captures at step 1, image 1 only replays
+    assert len(eng._graphs) == 1
+    got_sub = run(2, timesteps=[1, 3])       # two more signatures (selected / not selected)
+    for a, b in zip(got + [got_sub], ref + [ref_sub]):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7)
+    n = len(eng._graphs)
+    again = run(1)
+    assert len(eng._graphs) == n             # nothing re-captured
+    np.testing.assert_allclose(again, ref[1], rtol=1e-5, atol=1e-7)
+    # encode path: batches of new latents replay one graph
+    lat = [torch.randn(2, 16, 32, 32, generator=torch.Generator().manual_seed(i)) for i in range(3)]
+    enc = lambda l: pipe.encode_image(l, concepts[:2], width=256, height=256, layer_indices=[0, 2],
+                                      return_pil_heatmaps=False).concept_heatmaps
+    eng.use_graphs = False
+    ref_e = [enc(l) for l in lat]
+    eng.use_graphs = True
+    got_e = [enc(l) for l in lat]
+    for a, b in zip(got_e, ref_e):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7)
