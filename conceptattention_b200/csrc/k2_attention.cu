@@ -276,7 +276,7 @@ struct SmemV1 {
   uint8_t kv[kKvStages][kTileBytes];
   uint64_t q_full[2], kv_full[kKvStages], kv_empty[kKvStages], s_full[2], p_full[2], o_done;
   uint32_t tmem_base;
-  float xchg[2][2][kBM];        // v3: row max / row sum exchange between the two column halves
+  float xchg[2][2][2][kBM];     // v3/v4: [pair][parity][half][row] row max / row sum exchange
 };
 
 struct UnitV1 {
@@ -332,6 +332,9 @@ __device__ __forceinline__ void v1_producer(SmemV1& sm, const CUtensorMap* tmq,
   for (int j = 1; j < u.n_tiles; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
 }
 
+// kLean: the k-loops are not unrolled, so the issuing thread keeps one descriptor pair live
+// instead of sixteen (v4 leaves the control warpgroup 32 registers per thread).
+template <bool kLean>
 __device__ __forceinline__ void v1_mma(SmemV1& sm, uint32_t tmem, const UnitV1& u) {
   constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
   constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
@@ -342,20 +345,36 @@ __device__ __forceinline__ void v1_mma(SmemV1& sm, uint32_t tmem, const UnitV1& 
   };
   auto qk = [&](int t, int kslot) {                      // S_t = Q_t K^T
     const uint32_t qa = smem_u32(sm.q[t]), ka = smem_u32(sm.kv[kslot]);
+    if (kLean) {
+#pragma unroll 1
+      for (int kk = 0; kk < kD / 16; ++kk) {
+        const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+        mma_ss(tmem + t * 128, make_smem_desc(qa + off, 16, 1024), make_smem_desc(ka + off, 16, 1024),
+               idesc_qk, kk > 0);
+      }
+    } else {
 #pragma unroll
-    for (int kk = 0; kk < kD / 16; ++kk) {
-      const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
-      mma_ss(tmem + t * 128, make_smem_desc(qa + off, 16, 1024), make_smem_desc(ka + off, 16, 1024),
-             idesc_qk, kk > 0);
+      for (int kk = 0; kk < kD / 16; ++kk) {
+        const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+        mma_ss(tmem + t * 128, make_smem_desc(qa + off, 16, 1024), make_smem_desc(ka + off, 16, 1024),
+               idesc_qk, kk > 0);
+      }
     }
     mma_commit(&sm.s_full[t]);
   };
   auto pv = [&](int t, int vslot, bool acc) {            // O_t (+)= P_t V, P_t from TMEM
     const uint32_t va = smem_u32(sm.kv[vslot]);
+    if (kLean) {
+#pragma unroll 1
+      for (int kk = 0; kk < kBN / 16; ++kk)
+        mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kk * 8,
+               make_smem_desc(va + kk * 2048, kHalfBytes, 1024), idesc_pv, acc || kk > 0);
+    } else {
 #pragma unroll
-    for (int kk = 0; kk < kBN / 16; ++kk)
-      mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kk * 8,
-             make_smem_desc(va + kk * 2048, kHalfBytes, 1024), idesc_pv, acc || kk > 0);
+      for (int kk = 0; kk < kBN / 16; ++kk)
+        mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kk * 8,
+               make_smem_desc(va + kk * 2048, kHalfBytes, 1024), idesc_pv, acc || kk > 0);
+    }
   };
   const bool two = u.n_q == 2;
   mbar_wait(&sm.q_full[0], 0);
@@ -535,13 +554,19 @@ __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const Unit
 // (named barrier, 256 threads); that barrier also orders every S read of the tile before
 // any P write, which matters because P (columns [0,64)) overlays the columns warpgroup 0 reads.
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void softmax_bar_sync() {
-  asm volatile("bar.sync 1, 256;" ::: "memory");
+__device__ __forceinline__ void softmax_bar_sync(int id) {
+  asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory");
 }
 
-template <int kPolyEvery>
+// kTile = -1: v3, the 256 softmax threads walk tile 0 then tile 1 of every key step.
+// kTile = 0/1: v4, this 256-thread pair owns tile kTile only; the other pair (a second set of
+// two warpgroups) owns the other tile and runs concurrently, staggered by the MMA pipeline, so
+// each SM sub-partition holds four softmax warps in two different phases: one pair's
+// TMEM-load / max / exchange / pack / TMEM-store latency hides under the other's MUFU stream.
+template <int kPolyEvery, int kTile>
 __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const UnitV1& u,
                                            const AttnParams& p, int half, int b, int h) {
+  constexpr int kPair = kTile < 0 ? 0 : kTile;
   const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
   const int row = warp_q * 32 + lane;
   const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
@@ -565,9 +590,9 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
     return fmaxf(mx, fmaxf(m0, m1));
   };
   auto exchange = [&](float mine, bool take_max) {        // combine with the row's other thread
-    float* xb = &sm.xchg[use & 1][0][0];
+    float* xb = &sm.xchg[kPair][use & 1][0][0];
     xb[half * kBM + row] = mine;
-    softmax_bar_sync();
+    softmax_bar_sync(1 + kPair);
     const float other = xb[(half ^ 1) * kBM + row];
     ++use;
     return take_max ? fmaxf(mine, other) : mine + other;
@@ -578,7 +603,7 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
     int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
 #pragma unroll
     for (int t = 0; t < 2; ++t) {
-      if (t < u.n_q) {
+      if ((kTile < 0 || t == kTile) && t < u.n_q) {
         const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
         mbar_wait(&sm.s_full[t], j & 1);
         tc_fence_after();
@@ -596,14 +621,15 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
           // PV_t(j-1) has completed: the commit behind s_full[t] covers it.
           const float alpha = grow ? ex2((m_used[t] - m_new) * scale) : 1.f;
           l_sum[t] *= alpha;
+          // rare path: 8 columns at a time so it adds nothing to the loop's register budget
+#pragma unroll 1
+          for (int c = 0; c < 64; c += 8) {
+            uint32_t rc[8];
+            tmem_ld8(t_o + c0 + c, rc);
+            tmem_wait_ld8(rc);
 #pragma unroll
-          for (int c = 0; c < 64; c += 32) {
-            uint32_t rc[32];
-            tmem_ld32(t_o + c0 + c, rc);
-            tmem_wait_ld32(rc);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
-            tmem_st32(t_o + c0 + c, rc);
+            for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+            tmem_st8(t_o + c0 + c, rc);
           }
         }
         m_used[t] = m_new;
@@ -646,7 +672,7 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
   tc_fence_after();
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
-    if (t < u.n_q) {
+    if ((kTile < 0 || t == kTile) && t < u.n_q) {
       const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
       const float inv_l = 1.f / exchange(l_sum[t], false);
       const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
@@ -666,8 +692,10 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
   }
 }
 
-template <int kPolyEvery, bool kCoop>
-__global__ void __launch_bounds__(384, 1)
+// kMode 0: v1/v2 (one softmax warpgroup per tile), 1: v3 (two warpgroups, one tile at a time),
+// 2: v4 (four warpgroups = two column-half pairs, one pair per tile, 640 threads).
+template <int kPolyEvery, int kMode>
+__global__ void __launch_bounds__(kMode == 2 ? 640 : 384, 1)
 attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -680,7 +708,7 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
     prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
     mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
     for (int i = 0; i < kKvStages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], kCoop ? 8 : 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], kMode ? 8 : 4); }
     mbar_init(&sm.o_done, 1);
     fence_barrier_init();
   }
@@ -691,16 +719,23 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   const uint32_t tmem = sm.tmem_base;
 
   if (warp < 4) {
-    setmaxnreg_dec<96>();
+    if (kMode == 2) setmaxnreg_dec<32>(); else setmaxnreg_dec<96>();
     if (warp == 0) {
       if (elect_one()) v1_producer(sm, &tmq, &tmk, &tmv, u, bh);
     } else if (warp == 1) {
-      if (elect_one()) v1_mma(sm, tmem, u);
+      if (elect_one()) v1_mma<kMode == 2>(sm, tmem, u);
     }
+  } else if (kMode == 2) {
+    // setmaxnreg pool = what the CTA was launched with, 640 x 96 = 61440 = 4 x 32 x 32 + 16 x 32 x 112
+    // (asking for more blocks forever)
+    setmaxnreg_inc<112>();
+    const int pair = (warp - 4) >> 3, half = ((warp - 4) >> 2) & 1;
+    if (pair == 0) v3_softmax<kPolyEvery, 0>(sm, tmem, u, p, half, b, h);
+    else v3_softmax<kPolyEvery, 1>(sm, tmem, u, p, half, b, h);
   } else {
     setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
-    if (kCoop) v3_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+    if (kMode == 1) v3_softmax<kPolyEvery, -1>(sm, tmem, u, p, t, b, h);
     else if (t < u.n_q) v1_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
   }
   tc_fence_before();
@@ -788,14 +823,20 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
     const int units = (p.n_main_tiles + 1) / 2 + (concept_attn ? 1 : 0);
     if (units > 0) {
       const int smem = (int)sizeof(SmemV1) + 1024;
-      // impl 0: v3 (cooperating warpgroups), polynomial exp2 on every 4th element pair;
-      // 4 / 5: v3 with every 2nd pair / all MUFU; 2 / 3: v2 (one warpgroup per tile) all MUFU / every 4th
-      auto kern = g_attention_impl == 2 ? attn_v1_kernel<0, false>
-                : g_attention_impl == 3 ? attn_v1_kernel<4, false>
-                : g_attention_impl == 4 ? attn_v1_kernel<2, true>
-                : g_attention_impl == 5 ? attn_v1_kernel<0, true> : attn_v1_kernel<4, true>;
+      // impl 0: v3 (two cooperating warpgroups), polynomial exp2 on every 4th element pair;
+      // 4 / 5: v3 every 2nd pair / all MUFU; 2 / 3: v2 (one warpgroup per tile) all MUFU / every 4th;
+      // 9 / 6 / 7: v4 (four warpgroups, 640 threads) every 4th / every 2nd / all MUFU — measured
+      // 3-5 % slower than v3 on B200 (profiles/r01_k2_v4_experiment.md), kept for A/B runs.
+      auto kern = g_attention_impl == 2 ? attn_v1_kernel<0, 0>
+                : g_attention_impl == 3 ? attn_v1_kernel<4, 0>
+                : g_attention_impl == 4 ? attn_v1_kernel<2, 1>
+                : g_attention_impl == 5 ? attn_v1_kernel<0, 1>
+                : g_attention_impl == 9 ? attn_v1_kernel<4, 2>
+                : g_attention_impl == 6 ? attn_v1_kernel<2, 2>
+                : g_attention_impl == 7 ? attn_v1_kernel<0, 2> : attn_v1_kernel<4, 1>;
+      const bool v4 = g_attention_impl == 9 || g_attention_impl == 6 || g_attention_impl == 7;
       CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      kern<<<dim3(units, B * H), 384, smem, st>>>(tmq, tmk, tmv, p);
+      kern<<<dim3(units, B * H), v4 ? 640 : 384, smem, st>>>(tmq, tmk, tmv, p);
       CA_LAUNCH_CHECK();
     }
   }
