@@ -270,8 +270,9 @@ def run_ours(args, rank, world, local_rank):
                                f"{mode}: {nsteps if mode == 'generate' else 1} DiT pass(es) x ({blocks}), heatmaps from "
                                f"layers {layers[0]}..{layers[-1]} both spaces",
                    "images_per_step_per_gpu": batch,
-                   "parallelism": (f"heads sharded {H}/{world} per GPU, all-reduce of partial heatmap logits + "
-                                   f"all-gather of attention outputs (NCCL)") if sharded else
+                   "parallelism": (f"heads sharded {H}/{world} per GPU with the linears tensor-parallel around them; "
+                                   f"NCCL all-reduce of partial heatmap logits and of the row-parallel "
+                                   f"proj/MLP partial sums") if sharded else
                                   f"dp{world} (one image stream per GPU, no collective on the data path)",
                    "cache": "inputs larger than L2: 23.8 GB of bf16 weights stream through every step"},
         "e2e": {"value": images / (ms_e2e * 1e-3), "unit": "images/s",

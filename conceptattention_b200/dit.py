@@ -205,19 +205,36 @@ class FluxDiTEngine:
             self.mod_w[o:o + m].copy_(self.sd.pop(n + ".weight"))
             self.mod_b[o:o + m].copy_(self.sd.pop(n + ".bias"))
         if self.hs is not None and self.hs.world > 1:
-            rows = self.hs.qkv_rows(128).to(self.device)
-            for i in range(params.depth):
-                for st in ("img", "txt"):
-                    for kind in ("weight", "bias"):
-                        key = f"double_blocks.{i}.{st}_attn.qkv.{kind}"
-                        if key in self.sd:
-                            self.sd[key] = self.sd[key][rows].contiguous()
+            self.hs.shard_state_dict(self.sd, params)
         self._rope_cache = {}
         # CUDA graphs of whole forwards (one per signature), captured the second time a
         # signature is seen; the first call runs launch by launch and warms cuBLAS.
         self.use_graphs = True
         self.max_graphs = 8
         self._graphs, self._graph_seen, self._graph_pool = {}, {}, None
+
+    def _lin_rp(self, prefix, x, bias_key=None, extra=None):
+        """Row-parallel linear: y = x W^T (+ xe We^T) + b summed over the ranks; a plain linear
+        on one GPU.  `extra` = (xe, We) is a second accumulating GEMM (linear2 over
+        cat(attn, gelu(mlp)) without building the cat).  Sharded: W, We hold this rank's input
+        columns and b is zero on ranks > 0.  `hs.reduce_fp32` keeps the partial sums in fp32
+        through the all-reduce (one bf16 rounding, as on one GPU) at twice the NVLink bytes."""
+        w, b = self.sd[prefix + ".weight"], self.sd.get(bias_key or prefix + ".bias")
+        sharded = self.hs is not None and self.hs.world > 1
+        x2 = x.reshape(-1, x.shape[-1])
+        if sharded and self.hs.reduce_fp32:
+            y = torch.mm(x2, w.t(), out_dtype=torch.float32)
+            if extra is not None:
+                y += torch.mm(extra[0].reshape(-1, extra[0].shape[-1]), extra[1].t(), out_dtype=torch.float32)
+            if b is not None and self.hs.rank == 0:
+                y += b
+            return self.hs.all_reduce_sum(y).to(BF16).view(*x.shape[:-1], w.shape[0])
+        y = F.linear(x2, w, b)
+        if extra is not None:
+            y.addmm_(extra[0].reshape(-1, extra[0].shape[-1]), extra[1].t())
+        if sharded:
+            self.hs.all_reduce_sum(y)
+        return y.view(*x.shape[:-1], w.shape[0])
 
     # -- helpers ---------------------------------------------------------------------
     def _lin(self, prefix, x):
@@ -360,6 +377,8 @@ class FluxDiTEngine:
             return mods[rows, o:o + m]
 
         collected = {k: [] for k in VECTOR_KEYS} if collect_vectors else None
+        sharded = self.hs is not None and self.hs.world > 1
+        Hl = self.hs.h_local if sharded else H                   # heads computed on this rank
         for i in range(p.depth):
             pre = f"double_blocks.{i}"
             sel = collect_vectors or (accumulator is not None and accumulator.multiplicity(i) > 0)
@@ -369,39 +388,37 @@ class FluxDiTEngine:
             # LN + modulate, qkv GEMMs (concept rows ride on the txt GEMM)
             img_qkv = self._lin(pre + ".img_attn.qkv", ops.ln_modulate(x_img, img_mod, None, None, 0, D))
             tc_qkv = self._lin(pre + ".txt_attn.qkv", ops.ln_modulate(txtc, txt_mod, con_mod, T, 0, D))
-            Hl = H if self.hs is None else self.hs.h_local
             res = ops.qkv_prep(
                 img_qkv, tc_qkv,
                 (self.sd[pre + ".img_attn.norm.query_norm.scale"], self.sd[pre + ".img_attn.norm.key_norm.scale"]),
                 (self.sd[pre + ".txt_attn.norm.query_norm.scale"], self.sd[pre + ".txt_attn.norm.key_norm.scale"]),
                 rope, Hl, want_q_pre=sel)
             q, k, v = res[:3]
-            attn_img, attn_tc = ops.joint_attention(q, k, v, P, T, C, mode)
+            attn_img, attn_tc = ops.joint_attention(q, k, v, P, T, C, mode)     # this rank's heads
             q_pre = res[3] if sel else None
-            if self.hs is not None and self.hs.world > 1:
-                if sel and accumulator is not None and accumulator.multiplicity(i) > 0:
+            if sel and accumulator is not None and accumulator.multiplicity(i) > 0:
+                if sharded:
                     # partial logits over this rank's heads, ONE all-reduce for both spaces
                     part = torch.empty(2, B, C, P, device=dev, dtype=torch.float32)
                     ops.heatmap_logits(attn_img, attn_tc[:, T:], out=part[0])
                     ops.heatmap_logits(q_pre[:, :, :P], q_pre[:, :, P + T:], per_head=True, out=part[1])
                     accumulator.add_logits(i, self.hs.all_reduce_sum(part))
-                attn_img = self.hs.all_gather_heads(attn_img)
-                attn_tc = self.hs.all_gather_heads(attn_tc)
-                if collect_vectors:
-                    q_pre = self.hs.all_gather(q_pre, 1)
-            elif sel and accumulator is not None:
-                accumulator.add(i, attn_img, attn_tc[:, T:], q_pre, P, T)
+                else:
+                    accumulator.add(i, attn_img, attn_tc[:, T:], q_pre, P, T)
+            if sharded and collect_vectors:
+                q_pre = self.hs.all_gather(q_pre, 1)
             if sel and collect_vectors:
-                collected["output_space_concept_vectors"].append(attn_tc[:, T:].clone())
-                collected["output_space_image_vectors"].append(attn_img)
+                gather = (lambda t: self.hs.all_gather_heads(t)) if sharded else (lambda t: t)
+                collected["output_space_concept_vectors"].append(gather(attn_tc[:, T:].clone()))
+                collected["output_space_image_vectors"].append(gather(attn_img))
                 collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
                 collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
             # residual updates; concept rows use the txt weights with their own gates
             for x, attn, m0, m1, split, s in ((x_img, attn_img, img_mod, None, None, "img"),
                                               (txtc, attn_tc, txt_mod, con_mod, T, "txt")):
-                proj = self._lin(f"{pre}.{s}_attn.proj", attn)
+                proj = self._lin_rp(f"{pre}.{s}_attn.proj", attn)
                 h = ops.gate_residual_ln_modulate(x, proj, m0, m1, split, 2 * D, 3 * D, 4 * D)
-                h = self._lin(f"{pre}.{s}_mlp.2", self._lin_gelu(f"{pre}.{s}_mlp.0", h))
+                h = self._lin_rp(f"{pre}.{s}_mlp.2", self._lin_gelu(f"{pre}.{s}_mlp.0", h))
                 ops.gate_residual_ln_modulate(x, h, m0, m1, split, 5 * D, 0, 0, want_out=False)
         if collect_vectors:
             collected = {k: torch.stack(v, 0) for k, v in collected.items()}
@@ -414,22 +431,22 @@ class FluxDiTEngine:
         x = torch.cat((x_img, txtc[:, :T]), 1).contiguous()                      # [B,P+T,D]
         N = P + T
         rope_s = rope[:N].contiguous() if C > 0 else rope
-        M = int(D * p.mlp_ratio)
         for i in range(p.depth_single_blocks):
             pre = f"single_blocks.{i}"
             mod = mod_of(pre + ".modulation.lin", slice(0, B))                    # [B,3D] view
             xm = ops.ln_modulate(x, mod, None, None, 0, D)
-            h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3D]
-            g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M] gelu in epilogue
+            h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3*Hl*128]
+            g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M/G] gelu in epilogue
             q, k, v = ops.qkv_prep(h, None, (self.sd[pre + ".norm.query_norm.scale"],
-                                             self.sd[pre + ".norm.key_norm.scale"]), None, rope_s, H)
+                                             self.sd[pre + ".norm.key_norm.scale"]), None, rope_s, Hl)
             if B == 1:
-                attn = torch.empty(1, N, D, device=dev, dtype=BF16)
+                attn = torch.empty(1, N, Hl * 128, device=dev, dtype=BF16)
                 ops.joint_attention(q, k, v, P, T, 0, _cabi.ATTN_BOTH, attn[:, :P], attn[:, P:])
             else:
                 attn = torch.cat(ops.joint_attention(q, k, v, P, T, 0), 1)
-            out = F.linear(attn, self.sd[pre + ".linear2a.weight"], self.sd[pre + ".linear2.bias"])
-            out = out.view(-1, D).addmm_(g.view(-1, M), self.sd[pre + ".linear2b.weight"].t()).view(B, N, D)
+            # linear2 over cat(attn, gelu(mlp)) as two accumulating GEMMs (row-parallel when sharded)
+            out = self._lin_rp(pre + ".linear2a", attn, bias_key=pre + ".linear2.bias",
+                               extra=(g, self.sd[pre + ".linear2b.weight"]))
             ops.gate_residual_ln_modulate(x, out, mod, None, None, 2 * D, 0, 0, want_out=False)
         x = x[:, :P].contiguous()
         ada = mod_of("final_layer.adaLN_modulation.1", slice(0, B))               # [B,2D] shift|scale

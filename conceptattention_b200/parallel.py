@@ -11,8 +11,10 @@ Two modes:
 * head sharding — for very large token counts.  Attention is independent per head
   and the heatmap logits are a plain sum over H*d (concept_attention_pipeline.py:57-61),
   hence over heads; softmax over concepts is not linear so it comes after the sum.
-  `HeadShard` describes a rank's head slice and carries the two collectives the path
-  needs: all-gather of attention outputs over heads, all-reduce(SUM) of partial logits.
+  `HeadShard` describes a rank's head slice, shards the linears tensor-parallel around it
+  (column-parallel qkv / mlp.0, row-parallel proj / mlp.2 / linear2) and carries the
+  collective the path needs: all-reduce(SUM) of partial heatmap logits and of the
+  row-parallel partial outputs (all-gather only when the caller wants the raw vectors).
 """
 from __future__ import annotations
 
@@ -84,6 +86,7 @@ class HeadShard:
     world: int
     num_heads: int
     group: object = None
+    reduce_fp32: bool = False     # row-parallel partial sums all-reduced in fp32 (tight parity mode)
 
     def __post_init__(self):
         if self.num_heads % self.world:
@@ -99,6 +102,51 @@ class HeadShard:
         D = self.num_heads * head_dim
         cols = torch.arange(self.h0 * head_dim, self.h1 * head_dim)
         return torch.cat([cols + k * D for k in range(3)])
+
+    def shard_state_dict(self, sd: dict, params) -> dict:
+        """Tensor-parallel layout of the head-sharded mode (SURVEY.md 8e "shard linears
+        TP-style"), applied IN PLACE to an engine state dict (single-block linear1/linear2
+        already split into linear1q|linear1m and linear2a|linear2b):
+        qkv / linear1q keep the rows of this rank's heads and mlp.0 / linear1m a 1/G row slice
+        (column-parallel, no communication); proj / mlp.2 / linear2 keep the matching input
+        columns (row-parallel: partial [B,N,D] sums, one all-reduce each).  The bias of a
+        row-parallel linear is added on rank 0 only (zeroed elsewhere)."""
+        D = params.hidden_size
+        M = int(D * params.mlp_ratio)
+        if M % self.world:
+            raise ValueError(f"mlp width {M} does not split over {self.world} ranks")
+        d = D // self.num_heads
+        hcols = slice(self.h0 * d, self.h1 * d)
+        mcols = slice(self.rank * (M // self.world), (self.rank + 1) * (M // self.world))
+
+        def col_parallel(prefix, sel):
+            for kind in ("weight", "bias"):
+                key = f"{prefix}.{kind}"
+                if key in sd:
+                    idx = sel.to(sd[key].device) if isinstance(sel, torch.Tensor) else sel
+                    sd[key] = sd[key][idx].contiguous()
+
+        def row_parallel(prefix, sel, bias_key=None):
+            sd[prefix + ".weight"] = sd[prefix + ".weight"][:, sel].contiguous()
+            bias_key = bias_key or prefix + ".bias"
+            if self.rank > 0 and bias_key in sd:
+                sd[bias_key] = torch.zeros_like(sd[bias_key])
+
+        rows = self.qkv_rows(d)
+        for i in range(params.depth):
+            for st in ("img", "txt"):
+                pre = f"double_blocks.{i}.{st}"
+                col_parallel(pre + "_attn.qkv", rows)
+                row_parallel(pre + "_attn.proj", hcols)
+                col_parallel(pre + "_mlp.0", mcols)
+                row_parallel(pre + "_mlp.2", mcols)
+        for i in range(params.depth_single_blocks):
+            pre = f"single_blocks.{i}"
+            col_parallel(pre + ".linear1q", rows)
+            col_parallel(pre + ".linear1m", mcols)
+            row_parallel(pre + ".linear2a", hcols, bias_key=pre + ".linear2.bias")
+            sd[pre + ".linear2b.weight"] = sd[pre + ".linear2b.weight"][:, mcols].contiguous()
+        return sd
 
     # -- collectives ------------------------------------------------------------------
     def _gloo(self) -> bool:
@@ -132,8 +180,8 @@ class HeadShard:
     def all_reduce_sum(self, x: torch.Tensor) -> torch.Tensor:
         """In-place SUM over ranks (partial heatmap logits, fp32)."""
         if self.world > 1:
-            if self._gloo() and x.is_cuda:
-                h = x.cpu()
+            if self._gloo() and (x.is_cuda or x.dtype == torch.bfloat16):
+                h = x.float().cpu()               # gloo: host staging, fp32 arithmetic
                 dist.all_reduce(h, op=dist.ReduceOp.SUM, group=self.group)
                 x.copy_(h)
             else:

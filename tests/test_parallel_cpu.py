@@ -84,6 +84,49 @@ def test_head_shard_collectives_and_weight_slices():
         assert ret[r] == (True, True, True, True), (r, ret[r])
 
 
+def _tp_job(rank, world):
+    """Sharded linears reproduce the full ones: column-parallel then row-parallel MLP, the
+    head-sliced proj, and the single block's linear2 over cat(attn, gelu(mlp))."""
+    import torch.nn.functional as F
+    from conceptattention_b200.weights import CONFIGS, init_state_dict
+    p = CONFIGS["tiny"]
+    D, M, d = p.hidden_size, int(p.hidden_size * p.mlp_ratio), p.hidden_size // p.num_heads
+    full = init_state_dict(p, seed=3)
+    for i in range(p.depth_single_blocks):                # the engine's split of linear1 / linear2
+        w = full.pop(f"single_blocks.{i}.linear2.weight")
+        full[f"single_blocks.{i}.linear2a.weight"], full[f"single_blocks.{i}.linear2b.weight"] = w[:, :D], w[:, D:]
+        w1, b1 = full.pop(f"single_blocks.{i}.linear1.weight"), full.pop(f"single_blocks.{i}.linear1.bias")
+        full[f"single_blocks.{i}.linear1q.weight"], full[f"single_blocks.{i}.linear1q.bias"] = w1[:3 * D], b1[:3 * D]
+        full[f"single_blocks.{i}.linear1m.weight"], full[f"single_blocks.{i}.linear1m.bias"] = w1[3 * D:], b1[3 * D:]
+    hs = HeadShard(rank, world, p.num_heads)
+    mine = hs.shard_state_dict(dict(full), p)
+    g = torch.Generator().manual_seed(1)
+    x, attn = torch.randn(5, D, generator=g), torch.randn(5, D, generator=g)
+    lin = lambda sd, k, t: F.linear(t, sd[k + ".weight"], sd.get(k + ".bias"))
+    pre = "double_blocks.1.txt"
+    ref_mlp = lin(full, pre + "_mlp.2", F.gelu(lin(full, pre + "_mlp.0", x), approximate="tanh"))
+    got_mlp = hs.all_reduce_sum(lin(mine, pre + "_mlp.2", F.gelu(lin(mine, pre + "_mlp.0", x), approximate="tanh")))
+    ref_proj = lin(full, pre + "_attn.proj", attn)
+    got_proj = hs.all_reduce_sum(lin(mine, pre + "_attn.proj", attn[:, hs.h0 * d:hs.h1 * d]))
+    sp = "single_blocks.0"
+    gl = F.gelu(lin(full, sp + ".linear1m", x), approximate="tanh")
+    ref_l2 = F.linear(torch.cat((attn, gl), 1), torch.cat((full[sp + ".linear2a.weight"], full[sp + ".linear2b.weight"]), 1),
+                      full[sp + ".linear2.bias"])
+    part = F.linear(attn[:, hs.h0 * d:hs.h1 * d], mine[sp + ".linear2a.weight"], mine[sp + ".linear2.bias"])
+    part = part + F.gelu(lin(mine, sp + ".linear1m", x), approximate="tanh") @ mine[sp + ".linear2b.weight"].t()
+    got_l2 = hs.all_reduce_sum(part)
+    ok_bf16 = torch.allclose(hs.all_reduce_sum(torch.full((4,), 1.5, dtype=torch.bfloat16)),
+                             torch.full((4,), 1.5 * world, dtype=torch.bfloat16))
+    return tuple(torch.allclose(a, b, rtol=1e-4, atol=1e-5) for a, b in
+                 ((got_mlp, ref_mlp), (got_proj, ref_proj), (got_l2, ref_l2))) + (ok_bf16,)
+
+
+def test_tensor_parallel_linears_match_full():
+    ret = _run(_tp_job)
+    for r in (0, 1):
+        assert ret[r] == (True, True, True, True), (r, ret[r])
+
+
 def test_head_shard_rejects_uneven_split():
     import pytest
     with pytest.raises(ValueError):
