@@ -7,7 +7,8 @@ metric  : concept-heatmap images/sec @1024^2 Flux-schnell (configs[1] of BASELIN
           4096 image tokens, 256 text tokens, 4 concepts, 4 denoising steps, bf16,
           heatmaps from layers 15..18 of every step, both spaces).
 step    : one image = 4 x (19 double + 38 single blocks) + heatmap accumulation.
-value   : images/s with the step's inputs already resident in HBM (CUDA events).
+value   : images/s with the step's inputs already resident in HBM (CUDA events), kernels launched
+          one by one with a CUDA-event pair around every K2 launch (graph_replay: same, replayed).
 e2e     : images/s through ConceptAttentionFluxPipeline.generate_image with pinned
           HOST inputs (latents, text/concept embeddings) copied H2D and the heatmaps
           copied D2H inside the timed region.
@@ -179,7 +180,12 @@ def run_ours(args, rank, world, local_rank):
     for i in range(args.warmup):
         device_step(i)
     barrier()
+    # Timed region: K steps launch by launch with a CUDA-event pair around every K2 launch on
+    # its stream, so `roofline` is measured inside the region `value` is measured on.  (While
+    # ATTN_EVENTS is set the engine does not replay captured graphs: events recorded inside a
+    # graph cannot be read back.  The graph-replay number is reported beside it.)
     ops.LAUNCHES = 0
+    ops.ATTN_EVENTS = []
     clocks = ClockSampler(local_rank)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -192,22 +198,19 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.profiler.stop()
     ms_dev = e0.elapsed_time(e1)
     launches = ops.LAUNCHES
-    # roofline pass: the SAME K steps launch by launch, a CUDA-event pair around every K2 launch
-    # on its stream (events recorded inside a captured graph cannot be read back, so the engine
-    # does not replay graphs while ATTN_EVENTS is set).
-    ops.ATTN_EVENTS = []
+    attn_ms = sum(ev[0].elapsed_time(ev[1]) for ev, *_ in ops.ATTN_EVENTS)
+    n_attn = len(ops.ATTN_EVENTS)
+    attn_flops = sum(B * attention_flops(Pq, Tq, Cq, Hq, Cq > 0) for _, B, Pq, Tq, Cq, Hq in ops.ATTN_EVENTS)
+    ops.ATTN_EVENTS = None
+    # the same K steps as the product runs them by default (whole forwards replayed as CUDA graphs)
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     for i in range(args.steps):
         device_step(args.warmup + i)
     e3.record()
     barrier()
-    ms_eager = e2.elapsed_time(e3)
+    ms_graph = e2.elapsed_time(e3)
     clk = clocks.stop()
-    attn_ms = sum(ev[0].elapsed_time(ev[1]) for ev, *_ in ops.ATTN_EVENTS)
-    n_attn = len(ops.ATTN_EVENTS)
-    attn_flops = sum(B * attention_flops(Pq, Tq, Cq, Hq, Cq > 0) for _, B, Pq, Tq, Cq, Hq in ops.ATTN_EVENTS)
-    ops.ATTN_EVENTS = None
     graphed = gen.model.use_graphs and len(gen.model._graphs) > 0
 
     # ---- arm 2: end to end through the public API with host buffers ---------------------
@@ -248,9 +251,9 @@ def run_ours(args, rank, world, local_rank):
     d2h = 2 * batch * C * P * 4
 
     if world > 1:
-        t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms_dev, ms_e2e, ms_graph], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        ms_dev, ms_e2e = t.tolist()
+        ms_dev, ms_e2e, ms_graph = t.tolist()
     pk = peaks()
     ach = attn_flops / (attn_ms * 1e-3) / 1e12 if attn_ms > 0 else 0.0
     traffic = None
@@ -283,11 +286,11 @@ def run_ours(args, rank, world, local_rank):
                      "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
                      "frac": ach / pk["tflops"], "peak_source": pk["source"], "traffic": traffic,
                      "launches_timed": n_attn, "avg_launch_ms": attn_ms / max(n_attn, 1),
-                     "share_of_step": attn_ms / ms_eager,
-                     "timed_in": "launch-by-launch pass of the same K steps run right after the timed "
-                                 "region (CUDA events around each K2 launch on its stream)",
-                     "ms_per_step_launch_by_launch": ms_eager / args.steps},
-        "cuda_graphs": graphed,
+                     "share_of_step": attn_ms / ms_dev},
+        "graph_replay": {"enabled": graphed, "value": images / (ms_graph * 1e-3), "unit": "images/s",
+                         "ms_per_step": ms_graph / args.steps,
+                         "note": "same K steps, inputs resident, whole forwards replayed as CUDA graphs "
+                                 "(the default of the public API, used by e2e)"},
     }
     return line, out
 
