@@ -424,6 +424,15 @@ __device__ __forceinline__ void exp2_poly2(uint64_t x2, float& e0, float& e1) {
   e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(j1) << 23));
 }
 
+// Which of the 16 element pairs of a 32-column chunk take the FMA-pipe polynomial instead of
+// MUFU.EX2: kPolyEvery = n > 0 -> every n-th pair; -3 -> 3 of every 8 (the two pipes balance at
+// ~37 % when the scale / row-sum FMAs are counted); 0 -> none.
+template <int kPolyEvery>
+__device__ __forceinline__ constexpr bool use_poly(int i) {
+  return kPolyEvery > 0 ? (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1
+       : kPolyEvery == -3 ? ((i & 7) == 2 || (i & 7) == 5 || (i & 7) == 7) : false;
+}
+
 template <int kPolyEvery>
 __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const UnitV1& u,
                                            const AttnParams& p, int t, int b, int h) {
@@ -642,7 +651,7 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
           for (int i = 0; i < 16; ++i) {
             const uint64_t x2 = fma2(pk64(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), scale2, nmb2);
             float e0, e1;
-            if (kPolyEvery > 0 && (i % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1) {
+            if (use_poly<kPolyEvery>(i)) {
               exp2_poly2(x2, e0, e1);
             } else {
               float x0, x1;
@@ -693,7 +702,8 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
 }
 
 // kMode 0: v1/v2 (one softmax warpgroup per tile), 1: v3 (two warpgroups, one tile at a time),
-// 2: v4 (four warpgroups = two column-half pairs, one pair per tile, 640 threads).
+// 2: v4 (four warpgroups = two column-half pairs, one pair per tile, 640 threads; MMA issue loops
+// rolled — unrolled they spill at 32 registers and measured 5-20 % slower).
 template <int kPolyEvery, int kMode>
 __global__ void __launch_bounds__(kMode == 2 ? 640 : 384, 1)
 attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
@@ -825,6 +835,7 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
       const int smem = (int)sizeof(SmemV1) + 1024;
       // impl 0: v3 (two cooperating warpgroups), polynomial exp2 on every 4th element pair;
       // 4 / 5: v3 every 2nd pair / all MUFU; 2 / 3: v2 (one warpgroup per tile) all MUFU / every 4th;
+      // 10: v3 with 3 of every 8 pairs on the polynomial;
       // 9 / 6 / 7: v4 (four warpgroups, 640 threads) every 4th / every 2nd / all MUFU — measured
       // 3-5 % slower than v3 on B200 (profiles/r01_k2_v4_experiment.md), kept for A/B runs.
       auto kern = g_attention_impl == 2 ? attn_v1_kernel<0, 0>
@@ -832,6 +843,7 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
                 : g_attention_impl == 4 ? attn_v1_kernel<2, 1>
                 : g_attention_impl == 5 ? attn_v1_kernel<0, 1>
                 : g_attention_impl == 9 ? attn_v1_kernel<4, 2>
+                : g_attention_impl == 10 ? attn_v1_kernel<-3, 1>
                 : g_attention_impl == 6 ? attn_v1_kernel<2, 2>
                 : g_attention_impl == 7 ? attn_v1_kernel<0, 2> : attn_v1_kernel<4, 1>;
       const bool v4 = g_attention_impl == 9 || g_attention_impl == 6 || g_attention_impl == 7;
