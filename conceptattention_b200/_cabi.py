@@ -67,6 +67,8 @@ def load():
         fn.restype = _RESTYPES.get(name, C.c_int)
     lib.ca_debug_set_attention_impl.argtypes = [_i]
     lib.ca_debug_set_attention_impl.restype = None
+    lib.ca_debug_set_ln_impl.argtypes = [_i]
+    lib.ca_debug_set_ln_impl.restype = None
     lib.ca_debug_set_heatmap_impl.argtypes = [_i]
     lib.ca_debug_set_heatmap_impl.restype = None
     lib.ca_debug_set_heatmap_split.argtypes = [_i]

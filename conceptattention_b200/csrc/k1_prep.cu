@@ -6,10 +6,88 @@
 //   ca_gate_residual_ln_modulate   modified_double_stream_block.py:194-202
 //   ca_qkv_prep                    :91-92,97-98,103-104,110,125 + layers.py:63-84 + math.py:25-30
 #include "ca_common.cuh"
+#include "sm100_ptx.cuh"
+
+#include <algorithm>
 
 namespace ca {
 
+using namespace ptx;
+
 constexpr int kWarpsPerCta = 4;
+
+// ---- row maths shared by both LN kernels (so they stay bit-identical) -----------------------
+// A lane holds its share of a row as packed fp32 pairs (FADD2 / FFMA2: two elements per issue
+// slot).  chunk = 8 consecutive elements = 4 pairs; lane i owns chunks i, i+32, ...
+__device__ __forceinline__ void unpack8_pairs(const uint4& u, uint64_t* p) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    p[i] = pk64(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u));
+}
+__device__ __forceinline__ uint32_t pack_pair(uint64_t p) {
+  float lo, hi;
+  upk64(p, lo, hi);
+  return pack2(lo, hi);
+}
+// x' = bf16(x + gate*y) for one chunk, in place; returns the packed bf16 to store
+__device__ __forceinline__ uint4 residual_chunk(uint64_t* v, const uint4& yraw, const uint4& graw) {
+  uint64_t yp[4], gp[4];
+  unpack8_pairs(yraw, yp);
+  unpack8_pairs(graw, gp);
+  uint32_t w[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    w[j] = pack_pair(fma2(gp[j], yp[j], v[j]));
+    v[j] = pk64(__uint_as_float(w[j] << 16), __uint_as_float(w[j] & 0xffff0000u));
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+template <int NCH>
+__device__ __forceinline__ float row_sum(const uint64_t (&v)[NCH][4], int lane, int nchunks) {
+  uint64_t s2 = pk64(0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < NCH; ++k)
+    if (lane + k * 32 < nchunks) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) s2 = add2(s2, v[k][j]);
+    }
+  float a, b;
+  upk64(s2, a, b);
+  return warp_sum(a + b);
+}
+template <int NCH>
+__device__ __forceinline__ float row_sqdev(const uint64_t (&v)[NCH][4], float mean, int lane, int nchunks) {
+  const uint64_t nm2 = pk64(-mean, -mean);
+  uint64_t s2 = pk64(0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < NCH; ++k)
+    if (lane + k * 32 < nchunks) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { const uint64_t d = add2(v[k][j], nm2); s2 = fma2(d, d, s2); }
+    }
+  float a, b;
+  upk64(s2, a, b);
+  return warp_sum(a + b);
+}
+// out = (1+scale) * ((v - mean) * rstd) + shift as two FMAs per pair:
+//   t = v*rstd + (-mean*rstd);  o = t*a1 + sh      (a1 = 1+scale, sh = shift: fp32 pairs)
+__device__ __forceinline__ uint4 norm_chunk(const uint64_t* v, uint64_t rstd2, uint64_t nmr2,
+                                            const uint64_t* a1, const uint64_t* sh) {
+  uint32_t w[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) w[j] = pack_pair(fma2(fma2(v[j], rstd2, nmr2), a1[j], sh[j]));
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+// a1 / sh pairs of one chunk straight from the bf16 modulation row in global memory
+__device__ __forceinline__ void mod_chunk_global(const __nv_bfloat16* mod, int shift_off, int scale_off,
+                                                 int c, uint64_t* a1, uint64_t* sh) {
+  unpack8_pairs(*reinterpret_cast<const uint4*>(mod + shift_off + c * 8), sh);
+  unpack8_pairs(*reinterpret_cast<const uint4*>(mod + scale_off + c * 8), a1);
+  const uint64_t one2 = pk64(1.f, 1.f);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) a1[j] = add2(a1[j], one2);
+}
 
 // Row-wise LN + modulate.  One warp per row, the row lives in registers
 // (NCH 16-byte chunks per lane), so x is read exactly once.
@@ -27,50 +105,157 @@ ln_modulate_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restric
   const int nchunks = D >> 3;
   __nv_bfloat16* xr = x + (int64_t)row * D;
 
-  float v[NCH][8];
-  float sum = 0.f;
+  uint64_t v[NCH][4];
 #pragma unroll
   for (int i = 0; i < NCH; ++i) {
     const int c = lane + i * 32;
     if (c < nchunks) {
-      uint4 u = kResidual ? *reinterpret_cast<const uint4*>(xr + c * 8) : ld_stream16(xr + c * 8);
-      unpack8(u, v[i]);
+      const uint4 u = kResidual ? *reinterpret_cast<const uint4*>(xr + c * 8) : ld_stream16(xr + c * 8);
+      unpack8_pairs(u, v[i]);
       if (kResidual) {
-        float yv[8], gv[8];
-        unpack8(ld_stream16(y + (int64_t)row * y_stride + c * 8), yv);
-        unpack8(*reinterpret_cast<const uint4*>(mod + gate_off + c * 8), gv);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[i][j] = bf16_round(v[i][j] + gv[j] * yv[j]);
-        *reinterpret_cast<uint4*>(xr + c * 8) = pack8(v[i]);
+        *reinterpret_cast<uint4*>(xr + c * 8) = residual_chunk(
+            v[i], ld_stream16(y + (int64_t)row * y_stride + c * 8),
+            *reinterpret_cast<const uint4*>(mod + gate_off + c * 8));
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) sum += v[i][j];
     } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+      for (int j = 0; j < 4; ++j) v[i][j] = pk64(0.f, 0.f);
     }
   }
   if (out == nullptr) return;
-  const float mean = warp_sum(sum) / D;
-  float sq = 0.f;
-#pragma unroll
-  for (int i = 0; i < NCH; ++i) {
-    if (lane + i * 32 < nchunks) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { float d = v[i][j] - mean; sq += d * d; }
-    }
-  }
-  const float rstd = rsqrtf(warp_sum(sq) / D + 1e-6f);
+  const float mean = row_sum<NCH>(v, lane, nchunks) / D;
+  const float rstd = rsqrtf(row_sqdev<NCH>(v, mean, lane, nchunks) / D + 1e-6f);
+  const uint64_t rstd2 = pk64(rstd, rstd), nmr2 = pk64(-mean * rstd, -mean * rstd);
 #pragma unroll
   for (int i = 0; i < NCH; ++i) {
     const int c = lane + i * 32;
     if (c < nchunks) {
-      float sh[8], sc[8], o[8];
-      unpack8(*reinterpret_cast<const uint4*>(mod + shift_off + c * 8), sh);
-      unpack8(*reinterpret_cast<const uint4*>(mod + scale_off + c * 8), sc);
+      uint64_t a1[4], sh[4];
+      mod_chunk_global(mod, shift_off, scale_off, c, a1, sh);
+      *reinterpret_cast<uint4*>(out + (int64_t)row * D + c * 8) = norm_chunk(v[i], rstd2, nmr2, a1, sh);
+    }
+  }
+}
+
+// Streaming form of the same row-wise op for the large token streams.  Persistent: one CTA of
+// 16 warps per SM, CTA c owns the contiguous row range [c*rows/G, (c+1)*rows/G), its warps take
+// those rows round-robin.  Rows are staged through shared memory by the TMA engine
+// (cp.async.bulk 1-D, one mbarrier per slot): a warp copies its row smem -> registers, re-arms
+// the slot for its next row at once and computes while that load is in flight, so the bytes in
+// flight per SM (96-192 KB) do not depend on occupancy and the grid is exactly the SM count (no
+// wave tail).  When every row of the CTA uses the same modulation row (always true for the image
+// and single streams at B = 1), (1+scale) and shift are converted to fp32 once per CTA into
+// shared memory instead of once per row.  Same maths as ln_modulate_kernel: bit-identical.
+constexpr int kStreamWarps = 16;
+int g_ln_impl = 0;     // 0 = auto, 1 = one warp per row only, 2 = staged kernel wherever it applies
+
+template <int NCH, bool kResidual>
+__global__ void __launch_bounds__(kStreamWarps * 32, 1)
+ln_stream_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                 int64_t y_stride, __nv_bfloat16* __restrict__ out, int rows, int N, int D,
+                 const __nv_bfloat16* __restrict__ mod0, const __nv_bfloat16* __restrict__ mod1,
+                 int split, int64_t mod_stride, int gate_off, int shift_off, int scale_off,
+                 int slots) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t row_bytes = (uint32_t)D * 2u;
+  const uint32_t slot_bytes = row_bytes * (kResidual ? 2u : 1u);
+  // layout: [a1 fp32 D | sh fp32 D] (only with an output) | row slots | mbarriers
+  float* a1_s = reinterpret_cast<float*>(smem);
+  float* sh_s = a1_s + D;
+  uint8_t* slots_base = smem + (out != nullptr ? (size_t)D * 8 : 0);
+  uint8_t* wbase = slots_base + (size_t)warp * slots * slot_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(slots_base + (size_t)kStreamWarps * slots * slot_bytes) + warp * slots;
+  const int64_t r_begin = (int64_t)blockIdx.x * rows / gridDim.x;
+  const int64_t r_end = (int64_t)(blockIdx.x + 1) * rows / gridDim.x;
+  const int my_n = (int)((r_end - r_begin - warp + kStreamWarps - 1) / kStreamWarps);   // may be <= 0
+  const int nchunks = D >> 3;
+
+  auto issue = [&](int i) {                               // lane 0 only
+    const int slot = i % slots;
+    const int64_t row = r_begin + warp + (int64_t)kStreamWarps * i;
+    uint8_t* dst = wbase + (size_t)slot * slot_bytes;
+    mbar_expect_tx(&bars[slot], slot_bytes);
+    bulk_load_1d(dst, x + row * D, row_bytes, &bars[slot]);
+    if (kResidual) bulk_load_1d(dst + row_bytes, y + row * y_stride, row_bytes, &bars[slot]);
+  };
+  if (lane == 0) {
+    for (int s = 0; s < slots; ++s) mbar_init(&bars[s], 1);
+    fence_barrier_init();
+    fence_proxy_async_smem();
+    for (int i = 0; i < slots && i < my_n; ++i) issue(i);
+  }
+  // one modulation row for the whole CTA?  (first and last row in the same batch element and
+  // on the same side of `split`)
+  bool cached = false;
+  if (out != nullptr && r_end > r_begin) {
+    const int b0 = (int)(r_begin / N), b1 = (int)((r_end - 1) / N);
+    const int n0 = (int)(r_begin - (int64_t)b0 * N), n1 = (int)(r_end - 1 - (int64_t)b1 * N);
+    cached = b0 == b1 && (n0 < split) == (n1 < split);
+    if (cached) {
+      const __nv_bfloat16* mod = (n0 < split ? mod0 : mod1) + (int64_t)b0 * mod_stride;
+      for (int c = threadIdx.x; c < nchunks; c += blockDim.x) {
+        uint64_t a1[4], sh[4];
+        mod_chunk_global(mod, shift_off, scale_off, c, a1, sh);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = (1.f + sc[j]) * ((v[i][j] - mean) * rstd) + sh[j];
-      *reinterpret_cast<uint4*>(out + (int64_t)row * D + c * 8) = pack8(o);
+        for (int j = 0; j < 4; ++j) {
+          reinterpret_cast<uint64_t*>(a1_s)[c * 4 + j] = a1[j];
+          reinterpret_cast<uint64_t*>(sh_s)[c * 4 + j] = sh[j];
+        }
+      }
+    }
+  }
+  __syncthreads();                                        // cache + this warp's barriers visible
+
+  for (int i = 0; i < my_n; ++i) {
+    const int slot = i % slots;
+    const int64_t row = r_begin + warp + (int64_t)kStreamWarps * i;
+    const int b = (int)(row / N), n = (int)(row - (int64_t)b * N);
+    const __nv_bfloat16* mod = (n < split ? mod0 : mod1) + (int64_t)b * mod_stride;
+    const uint8_t* src = wbase + (size_t)slot * slot_bytes;
+    mbar_wait(&bars[slot], (i / slots) & 1);
+
+    uint64_t v[NCH][4];
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+      const int c = lane + k * 32;
+      if (c < nchunks) {
+        unpack8_pairs(*reinterpret_cast<const uint4*>(src + c * 16), v[k]);
+        if (kResidual) {
+          *reinterpret_cast<uint4*>(x + row * D + c * 8) = residual_chunk(
+              v[k], *reinterpret_cast<const uint4*>(src + row_bytes + c * 16),
+              *reinterpret_cast<const uint4*>(mod + gate_off + c * 8));
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[k][j] = pk64(0.f, 0.f);
+      }
+    }
+    __syncwarp();                                         // every lane has read the slot
+    if (lane == 0 && i + slots < my_n) { fence_proxy_async_smem(); issue(i + slots); }
+    if (out == nullptr) continue;
+
+    const float mean = row_sum<NCH>(v, lane, nchunks) / D;
+    const float rstd = rsqrtf(row_sqdev<NCH>(v, mean, lane, nchunks) / D + 1e-6f);
+    const uint64_t rstd2 = pk64(rstd, rstd), nmr2 = pk64(-mean * rstd, -mean * rstd);
+#pragma unroll
+    for (int k = 0; k < NCH; ++k) {
+      const int c = lane + k * 32;
+      if (c < nchunks) {
+        uint64_t a1[4], sh[4];
+        if (cached) {
+          const ulonglong2 a_lo = *reinterpret_cast<const ulonglong2*>(a1_s + c * 8);
+          const ulonglong2 a_hi = *reinterpret_cast<const ulonglong2*>(a1_s + c * 8 + 4);
+          const ulonglong2 s_lo = *reinterpret_cast<const ulonglong2*>(sh_s + c * 8);
+          const ulonglong2 s_hi = *reinterpret_cast<const ulonglong2*>(sh_s + c * 8 + 4);
+          a1[0] = a_lo.x; a1[1] = a_lo.y; a1[2] = a_hi.x; a1[3] = a_hi.y;
+          sh[0] = s_lo.x; sh[1] = s_lo.y; sh[2] = s_hi.x; sh[3] = s_hi.y;
+        } else {
+          mod_chunk_global(mod, shift_off, scale_off, c, a1, sh);
+        }
+        *reinterpret_cast<uint4*>(out + row * D + c * 8) = norm_chunk(v[k], rstd2, nmr2, a1, sh);
+      }
     }
   }
 }
@@ -89,6 +274,45 @@ static ca_status launch_ln(void* x, const void* y, int64_t y_stride, void* out, 
   const int rows = B * N;
   if (rows == 0) return CA_OK;
   const int nch = (D / 8 + 31) / 32;
+  // Large token streams: persistent TMA-staged kernel, grid = SM count.  Small ones (the
+  // text+concept rows) and rows too wide for the staging buffers keep the one-warp-per-row form.
+  const size_t slot_bytes = (size_t)D * 2 * (kResidual ? 2 : 1);
+  const size_t cache_bytes = out ? (size_t)D * 8 : 0;             // fp32 (1+scale) and shift
+  const size_t budget = 226u * 1024u - cache_bytes;                // 227 KB per CTA on sm_100
+  const int slots = (int)std::min<size_t>(2, budget / (kStreamWarps * (slot_bytes + 8) + 256));
+  // Measured on B200 (scripts/bench_k1.py): the plain LN (one input stream) is faster in the
+  // one-warp-per-row form (0.70 vs 0.60 of HBM at 16 K rows); the residual forms (two input
+  // streams, in-place update) are faster staged (0.74 / 0.79 vs 0.65 / 0.61).  impl 2 forces
+  // the staged kernel for every form (tests).
+  const bool stream = g_ln_impl == 2 || (g_ln_impl == 0 && kResidual);
+  if (stream && rows >= 1024 && slots >= 1 && nch <= 16) {
+    static int sm_count = 0;
+    if (sm_count == 0) {
+      int dev = 0;
+      CA_CUDA_OK(cudaGetDevice(&dev));
+      CA_CUDA_OK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int grid_s = std::min(sm_count, (rows + kStreamWarps - 1) / kStreamWarps);
+    const int smem = (int)(cache_bytes + kStreamWarps * slots * (slot_bytes + 8) + 256);
+#define CA_LNS_CASE(NCH)                                                                          \
+  do {                                                                                            \
+    auto kern = ln_stream_kernel<NCH, kResidual>;                                                 \
+    CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));    \
+    kern<<<grid_s, kStreamWarps * 32, smem, st>>>(                                                \
+        (__nv_bfloat16*)x, (const __nv_bfloat16*)y, y_stride, (__nv_bfloat16*)out, rows, N, D,    \
+        (const __nv_bfloat16*)mod0, (const __nv_bfloat16*)mod1, split, mod_stride, gate_off,      \
+        shift_off, scale_off, slots);                                                             \
+  } while (0)
+    if (nch <= 1) CA_LNS_CASE(1);
+    else if (nch <= 2) CA_LNS_CASE(2);
+    else if (nch <= 4) CA_LNS_CASE(4);
+    else if (nch <= 8) CA_LNS_CASE(8);
+    else if (nch <= 12) CA_LNS_CASE(12);
+    else CA_LNS_CASE(16);
+#undef CA_LNS_CASE
+    CA_LAUNCH_CHECK();
+    return CA_OK;
+  }
   dim3 grid((rows + kWarpsPerCta - 1) / kWarpsPerCta), block(kWarpsPerCta * 32);
 #define CA_LN_CASE(NCH)                                                                         \
   ln_modulate_kernel<NCH, kResidual><<<grid, block, 0, st>>>(                                   \
@@ -184,6 +408,8 @@ qkv_prep_kernel(const __nv_bfloat16* __restrict__ qkv_a, int64_t stride_a, int N
 }
 
 }  // namespace ca
+
+extern "C" void ca_debug_set_ln_impl(int impl) { ca::g_ln_impl = impl; }
 
 extern "C" ca_status ca_ln_modulate(const void* x, void* out, int B, int N, int D, const void* mod0,
                                     const void* mod1, int split, int64_t mod_stride,

@@ -372,22 +372,26 @@ class FluxDiTEngine:
         svec = F.silu(torch.cat((vec, cvec), 0))                                  # [2B,D]
         mods = F.linear(svec, self.mod_w, self.mod_b)                             # [2B,Mtot]
 
-        def mod_of(name, rows):
-            o, m = self.mod_off[name]
-            return mods[rows, o:o + m]
+        # every kernel addresses its modulation chunks by ABSOLUTE column offset into `mods`:
+        # rows [0,B) come from vec (img / txt / single streams), rows [B,2B) from concept_vec
+        m_vec, m_con = mods[:B], mods[B:]
+        off = lambda name: self.mod_off[name][0]
 
         collected = {k: [] for k in VECTOR_KEYS} if collect_vectors else None
         sharded = self.hs is not None and self.hs.world > 1
         Hl = self.hs.h_local if sharded else H                   # heads computed on this rank
+        # LN + modulate of block 0; later blocks get theirs fused into the previous block's last
+        # gated-residual kernel (K1c with the NEXT block's shift/scale): one pass over x less per
+        # block boundary
+        o_i, o_t = off("double_blocks.0.img_mod.lin"), off("double_blocks.0.txt_mod.lin")
+        ln = {"img": ops.ln_modulate(x_img, m_vec, None, None, o_i, o_i + D),
+              "txt": ops.ln_modulate(txtc, m_vec, m_con, T, o_t, o_t + D)}
         for i in range(p.depth):
             pre = f"double_blocks.{i}"
             sel = collect_vectors or (accumulator is not None and accumulator.multiplicity(i) > 0)
-            img_mod = mod_of(pre + ".img_mod.lin", slice(0, B))                   # [B,6D] views
-            txt_mod = mod_of(pre + ".txt_mod.lin", slice(0, B))
-            con_mod = mod_of(pre + ".txt_mod.lin", slice(B, 2 * B))
-            # LN + modulate, qkv GEMMs (concept rows ride on the txt GEMM)
-            img_qkv = self._lin(pre + ".img_attn.qkv", ops.ln_modulate(x_img, img_mod, None, None, 0, D))
-            tc_qkv = self._lin(pre + ".txt_attn.qkv", ops.ln_modulate(txtc, txt_mod, con_mod, T, 0, D))
+            # qkv GEMMs (concept rows ride on the txt GEMM)
+            img_qkv = self._lin(pre + ".img_attn.qkv", ln["img"])
+            tc_qkv = self._lin(pre + ".txt_attn.qkv", ln["txt"])
             res = ops.qkv_prep(
                 img_qkv, tc_qkv,
                 (self.sd[pre + ".img_attn.norm.query_norm.scale"], self.sd[pre + ".img_attn.norm.key_norm.scale"]),
@@ -414,12 +418,16 @@ class FluxDiTEngine:
                 collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
                 collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
             # residual updates; concept rows use the txt weights with their own gates
-            for x, attn, m0, m1, split, s in ((x_img, attn_img, img_mod, None, None, "img"),
-                                              (txtc, attn_tc, txt_mod, con_mod, T, "txt")):
+            for x, attn, m1, split, s in ((x_img, attn_img, None, None, "img"), (txtc, attn_tc, m_con, T, "txt")):
+                o = off(f"{pre}.{s}_mod.lin")
                 proj = self._lin_rp(f"{pre}.{s}_attn.proj", attn)
-                h = ops.gate_residual_ln_modulate(x, proj, m0, m1, split, 2 * D, 3 * D, 4 * D)
+                h = ops.gate_residual_ln_modulate(x, proj, m_vec, m1, split, o + 2 * D, o + 3 * D, o + 4 * D)
                 h = self._lin_rp(f"{pre}.{s}_mlp.2", self._lin_gelu(f"{pre}.{s}_mlp.0", h))
-                ops.gate_residual_ln_modulate(x, h, m0, m1, split, 5 * D, 0, 0, want_out=False)
+                if i + 1 < p.depth:
+                    on = off(f"double_blocks.{i + 1}.{s}_mod.lin")
+                    ln[s] = ops.gate_residual_ln_modulate(x, h, m_vec, m1, split, o + 5 * D, on, on + D)
+                else:
+                    ops.gate_residual_ln_modulate(x, h, m_vec, m1, split, o + 5 * D, 0, 0, want_out=False)
         if collect_vectors:
             collected = {k: torch.stack(v, 0) for k, v in collected.items()}
         else:
@@ -431,10 +439,11 @@ class FluxDiTEngine:
         x = torch.cat((x_img, txtc[:, :T]), 1).contiguous()                      # [B,P+T,D]
         N = P + T
         rope_s = rope[:N].contiguous() if C > 0 else rope
+        o = off("single_blocks.0.modulation.lin") if p.depth_single_blocks else 0
+        xm = ops.ln_modulate(x, m_vec, None, None, o, o + D) if p.depth_single_blocks else None
         for i in range(p.depth_single_blocks):
             pre = f"single_blocks.{i}"
-            mod = mod_of(pre + ".modulation.lin", slice(0, B))                    # [B,3D] view
-            xm = ops.ln_modulate(x, mod, None, None, 0, D)
+            o = off(pre + ".modulation.lin")
             h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3*Hl*128]
             g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M/G] gelu in epilogue
             q, k, v = ops.qkv_prep(h, None, (self.sd[pre + ".norm.query_norm.scale"],
@@ -447,10 +456,14 @@ class FluxDiTEngine:
             # linear2 over cat(attn, gelu(mlp)) as two accumulating GEMMs (row-parallel when sharded)
             out = self._lin_rp(pre + ".linear2a", attn, bias_key=pre + ".linear2.bias",
                                extra=(g, self.sd[pre + ".linear2b.weight"]))
-            ops.gate_residual_ln_modulate(x, out, mod, None, None, 2 * D, 0, 0, want_out=False)
+            if i + 1 < p.depth_single_blocks:
+                on = off(f"single_blocks.{i + 1}.modulation.lin")
+                xm = ops.gate_residual_ln_modulate(x, out, m_vec, None, None, o + 2 * D, on, on + D)
+            else:
+                ops.gate_residual_ln_modulate(x, out, m_vec, None, None, o + 2 * D, 0, 0, want_out=False)
         x = x[:, :P].contiguous()
-        ada = mod_of("final_layer.adaLN_modulation.1", slice(0, B))               # [B,2D] shift|scale
-        pred = self._lin("final_layer.linear", ops.ln_modulate(x, ada, None, None, 0, D))
+        o = off("final_layer.adaLN_modulation.1")                                 # shift | scale
+        pred = self._lin("final_layer.linear", ops.ln_modulate(x, m_vec, None, None, o, o + D))
         return pred, collected
 
     __call__ = forward

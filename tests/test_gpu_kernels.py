@@ -69,6 +69,42 @@ def test_gate_residual_ln_modulate(ops, B, N, D, split, want_out):
         assert out is None
 
 
+@pytest.mark.parametrize("B,N,D,split", [(1, 4096, 3072, None), (2, 1111, 3072, 1000), (3, 700, 256, 650),
+                                         (1, 1025, 1032, 7)])
+def test_ln_streaming_kernels_match_row_kernels_and_oracle(ops, B, N, D, split):
+    """Large token streams take the persistent TMA-staged kernels (rows >= 1024); they must
+    agree BIT FOR BIT with the one-warp-per-row kernels (same summation order) and, through
+    them, with the oracle: ragged row counts per CTA/warp, B > 1, the per-row modulation
+    switch at `split`, a strided y (column slice of a wider matrix), and the no-LN form."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    x, y = rnd(B, N, D, seed=11, scale=2.0).cuda(), rnd(B, N, 2 * D, seed=12).cuda()[:, :, D:]
+    mod0, mod1 = rnd(B, 6 * D, seed=13, scale=0.5).cuda(), rnd(B, 6 * D, seed=14, scale=0.5).cuda()
+    m1 = None if split is None else mod1
+    res = {}
+    for impl in (1, 2):
+        lib.ca_debug_set_ln_impl(impl)
+        try:
+            a = ops.ln_modulate(x, mod0, m1, split, 0, D)
+            xb = x.clone()
+            b = ops.gate_residual_ln_modulate(xb, y, mod0, m1, split, 2 * D, 3 * D, 4 * D)
+            xc = x.clone()
+            ops.gate_residual_ln_modulate(xc, y, mod0, m1, split, 5 * D, 0, 0, want_out=False)
+            torch.cuda.synchronize()
+        finally:
+            lib.ca_debug_set_ln_impl(0)
+        res[impl] = (a, b, xb, xc)
+    for got, ref in zip(res[2], res[1]):
+        assert torch.equal(got, ref)
+    s_ = N if split is None else split
+    xf = x.float().cpu()
+    ref = torch.empty_like(xf)
+    for m, sl in ((mod0, slice(0, s_)), (mod1, slice(s_, N))):
+        mf = m.float().cpu()[:, None, :]
+        ref[:, sl] = oracle.layer_norm_modulate(xf[:, sl], mf[..., :D], mf[..., D:2 * D])
+    close(res[2][0], ref, rtol=1e-2, atol=2e-2)
+
+
 # ---------------------------------------------------------------- K1b
 @pytest.mark.parametrize("B,Na,Nb,H,extra", [(1, 144, 75, 2, 0), (2, 64, 20, 3, 0), (1, 100, 0, 2, 512)])
 def test_qkv_prep(ops, B, Na, Nb, H, extra):
