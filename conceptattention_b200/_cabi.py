@@ -28,6 +28,8 @@ SIGNATURES = {
     "ca_gate_residual_ln_modulate": [_p, _p, _i64, _p, _i, _i, _i, _p, _p, _i, _i64, _i, _i, _i, _p],
     "ca_qkv_prep": [_p, _i64, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p],
     "ca_joint_attention": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p],
+    "ca_joint_attention_workspace_bytes": [_i] * 6,
+    "ca_joint_attention_ws": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, C.c_size_t, _p],
     "ca_heatmap_accumulate": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p],
     "ca_heatmap_logits": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _p, _p],
     "ca_norm_accumulate": [_p, _i, _i, _i, _i, _i, _p, _p],
@@ -38,7 +40,8 @@ SIGNATURES = {
     "ca_binary_masks": [_p, _p, _i, _i, _p],
     "ca_heatmaps_from_vectors_host": [_p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _i, _i, _p],
 }
-_RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p}
+_RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p,
+             "ca_joint_attention_workspace_bytes": C.c_size_t}
 
 _lib = None
 
@@ -67,6 +70,8 @@ def load():
         fn.restype = _RESTYPES.get(name, C.c_int)
     lib.ca_debug_set_attention_impl.argtypes = [_i]
     lib.ca_debug_set_attention_impl.restype = None
+    lib.ca_debug_set_attention_streamk.argtypes = [_i]
+    lib.ca_debug_set_attention_streamk.restype = None
     lib.ca_debug_set_ln_impl.argtypes = [_i]
     lib.ca_debug_set_ln_impl.restype = None
     lib.ca_debug_set_heatmap_impl.argtypes = [_i]

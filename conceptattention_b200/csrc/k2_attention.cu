@@ -37,7 +37,22 @@ struct AttnParams {
   __nv_bfloat16* out_img;              // [B,P,H*128]
   __nv_bfloat16* out_txtc;             // [B,T+C,H*128]
   float scale_log2;                    // log2(e)/sqrt(128)
+  // flat 1-D grid: [ concept units | whole main units | stream-K tail pieces ] — the concept units
+  // (one 128-row tile over all P+C keys: long and not splittable here) start first, the short tail
+  // pieces fill the SMs last
+  int n_pairs;                         // main units (query-tile pairs) per (b,h)
+  int n_dp;                            // main units run whole, one CTA each
+  int sk_units;                        // tail main units whose key steps are spread over sk_sms ranges
+  int sk_sms;                          // number of ranges (2 CTAs per range, possibly empty); 0 = no split
+  int n_concept;                       // concept units (one per (b,h)) or 0
+  float* ws_part;                      // [2*sk_sms] partial slots (kPartFloats each)
+  int* ws_count;                       // [sk_units] arrival counters (zeroed by the launcher)
 };
+
+// one partial slot: per query tile an unnormalised fp32 O (stored [col/4][row][4] so that the 32
+// rows of a warp form 512-byte runs), the row max it is scaled to and the row sum
+constexpr int kPartTile = kBM * kD + 2 * kBM;
+constexpr int kPartFloats = 2 * kPartTile;
 
 // Key ranges visible to a query tile: up to two half-open row segments.
 struct KeySegs { int s0, e0, s1, e1; };
@@ -284,28 +299,76 @@ struct UnitV1 {
   int n_q;            // query tiles in this CTA (1 or 2)
   int q_row0[2], q_rows[2];
   KeySegs ks;
-  int n0, n_tiles;
+  int n0, n_tiles;    // key tiles of the unit: n0 in the first segment, n_tiles in total
+  int bh;
+  int j_begin, n_local;   // key tiles [j_begin, j_begin + n_local) are processed by this CTA
+  int part_slot;      // >= 0: write a partial into this slot and take part in the fix-up
+  int sk_unit;        // index of the tail unit (fix-up bookkeeping)
 };
 
-__device__ __forceinline__ UnitV1 decode_unit(const AttnParams& p, int unit) {
+// tail range i covers key steps [lo, hi) of the concatenated tail units (n steps each)
+__device__ __forceinline__ void sk_range(const AttnParams& p, int n, int i, int64_t& lo, int64_t& hi) {
+  const int64_t total = (int64_t)p.sk_units * n;
+  lo = (int64_t)i * total / p.sk_sms;
+  hi = (int64_t)(i + 1) * total / p.sk_sms;
+}
+// piece k (0/1) of range i: [lo, hi) clipped to the first / second unit it touches
+__device__ __forceinline__ bool sk_piece(const AttnParams& p, int n, int i, int k, int& unit,
+                                         int& j_begin, int& n_local) {
+  int64_t lo, hi;
+  sk_range(p, n, i, lo, hi);
+  if (lo >= hi) return false;
+  const int64_t a0 = lo / n, cut = (a0 + 1) * n;
+  int64_t s0, s1;
+  if (k == 0) { s0 = lo; s1 = hi < cut ? hi : cut; unit = (int)a0; }
+  else        { s0 = cut; s1 = hi; unit = (int)a0 + 1; }
+  if (s0 >= s1) return false;
+  j_begin = (int)(s0 - (int64_t)unit * n);
+  n_local = (int)(s1 - s0);
+  return true;
+}
+
+__device__ __forceinline__ UnitV1 decode_unit(const AttnParams& p, int cta) {
   UnitV1 u;
   const int PT = p.P + p.T;
-  const int n_pairs = (p.n_main_tiles + 1) >> 1;
-  u.concept_tile = unit >= n_pairs;
+  const int n_seg = 2 * p.sk_sms;
+  u.part_slot = -1; u.sk_unit = -1; u.j_begin = 0;
+  (void)n_seg;
+  u.concept_tile = cta < p.n_concept;
+  int unit = 0;                                           // main unit index over all (b,h)
+  bool empty = false;
   if (u.concept_tile) {
+    u.bh = cta;
     u.n_q = 1;
     u.q_row0[0] = PT; u.q_rows[0] = p.C; u.q_row0[1] = PT; u.q_rows[1] = 0;
   } else {
-    u.n_q = min(2, p.n_main_tiles - 2 * unit);
+    const int n_main = tiles_of(0, PT);
+    cta -= p.n_concept;
+    if (cta < p.n_dp) {
+      unit = cta;
+      u.n_local = n_main;
+    } else {
+      const int s = cta - p.n_dp;
+      int a = 0;
+      empty = !sk_piece(p, n_main, s >> 1, s & 1, a, u.j_begin, u.n_local);
+      unit = p.n_dp + a;
+      u.sk_unit = a;
+      if (!empty && !(u.j_begin == 0 && u.n_local == n_main)) u.part_slot = s;
+    }
+    u.bh = unit / p.n_pairs;
+    const int pair = unit - u.bh * p.n_pairs;
+    u.n_q = min(2, p.n_main_tiles - 2 * pair);
 #pragma unroll
     for (int t = 0; t < 2; ++t) {
-      u.q_row0[t] = (2 * unit + t) * kBM;
+      u.q_row0[t] = (2 * pair + t) * kBM;
       u.q_rows[t] = max(0, min(kBM, PT - u.q_row0[t]));
     }
   }
   u.ks = key_segments(p, u.concept_tile);
   u.n0 = tiles_of(u.ks.s0, u.ks.e0);
   u.n_tiles = u.n0 + tiles_of(u.ks.s1, u.ks.e1);
+  if (u.concept_tile) u.n_local = u.n_tiles;
+  if (empty) u.n_local = 0;
   return u;
 }
 
@@ -319,7 +382,7 @@ __device__ __forceinline__ void v1_producer(SmemV1& sm, const CUtensorMap* tmq,
     tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
   };
   auto load_kv = [&](const CUtensorMap* tm, int j) {
-    int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
     const int slot = item % kKvStages;
     mbar_wait(&sm.kv_empty[slot], ((item / kKvStages) & 1) ^ 1);
     load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
@@ -329,7 +392,7 @@ __device__ __forceinline__ void v1_producer(SmemV1& sm, const CUtensorMap* tmq,
   load_kv(tmk, 0);
   if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
   load_kv(tmv, 0);
-  for (int j = 1; j < u.n_tiles; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
+  for (int j = 1; j < u.n_local; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
 }
 
 // kLean: the k-loops are not unrolled, so the issuing thread keeps one descriptor pair live
@@ -383,8 +446,8 @@ __device__ __forceinline__ void v1_mma(SmemV1& sm, uint32_t tmem, const UnitV1& 
   qk(0, ks);
   if (two) { mbar_wait(&sm.q_full[1], 0); tc_fence_after(); qk(1, ks); }
   mma_commit(&sm.kv_empty[ks]);
-  for (int j = 0; j < u.n_tiles; ++j) {
-    const bool has_next = j + 1 < u.n_tiles;
+  for (int j = 0; j < u.n_local; ++j) {
+    const bool has_next = j + 1 < u.n_local;
     const int vs = kv_wait(2 * j + 1);
     if (has_next) ks = kv_wait(2 * j + 2);
     mbar_wait(&sm.p_full[0], j & 1);
@@ -464,8 +527,8 @@ __device__ __forceinline__ void v1_softmax(SmemV1& sm, uint32_t tmem, const Unit
   };
 
 #pragma unroll 1
-  for (int j = 0; j < u.n_tiles; ++j) {
-    int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
+  for (int j = 0; j < u.n_local; ++j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
     mbar_wait(&sm.s_full[t], j & 1);
     tc_fence_after();
     uint32_t ra[32], rb[32];
@@ -608,8 +671,8 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
   };
 
 #pragma unroll 1
-  for (int j = 0; j < u.n_tiles; ++j) {
-    int row0, valid; key_tile(u.ks, u.n0, j, row0, valid);
+  for (int j = 0; j < u.n_local; ++j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
 #pragma unroll
     for (int t = 0; t < 2; ++t) {
       if ((kTile < 0 || t == kTile) && t < u.n_q) {
@@ -679,26 +742,118 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
   // ---- epilogue: O_t / l -> bf16 "B L (H D)"; this thread owns columns [c0, c0+64) -------
   mbar_wait(&sm.o_done, 0);
   tc_fence_after();
+  if (u.part_slot < 0) {
 #pragma unroll
-  for (int t = 0; t < 2; ++t) {
-    if ((kTile < 0 || t == kTile) && t < u.n_q) {
-      const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
-      const float inv_l = 1.f / exchange(l_sum[t], false);
-      const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+    for (int t = 0; t < 2; ++t) {
+      if ((kTile < 0 || t == kTile) && t < u.n_q) {
+        const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
+        const float inv_l = 1.f / exchange(l_sum[t], false);
+        const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
 #pragma unroll
-      for (int c = 0; c < 64; c += 32) {
-        uint32_t r[32];
-        tmem_ld32(t_o + c0 + c, r);
-        tmem_wait_ld32(r);
-        if (row < q_rows) {
-          float o[32];
+        for (int c = 0; c < 64; c += 32) {
+          uint32_t r[32];
+          tmem_ld32(t_o + c0 + c, r);
+          tmem_wait_ld32(r);
+          if (row < q_rows) {
+            float o[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
-          store_out_row(p, b, h, q_row0 + row, o, inv_l, c0 + c, 32);
+            for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+            store_out_row(p, b, h, q_row0 + row, o, inv_l, c0 + c, 32);
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- stream-K piece: this CTA saw only key tiles [j_begin, j_begin + n_local) of its unit.
+  // Write (O unnormalised, row max, row sum) to the piece's slot; the piece that arrives last
+  // (atomic ticket, no waiting) merges all pieces of the unit in a fixed order and stores.
+  if (kTile >= 0) return;                                 // only the v3 layout takes part
+  const int n_main = p.n_main_tiles;
+  {
+    float* slot = p.ws_part + (size_t)u.part_slot * kPartFloats;
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      if (t < u.n_q) {
+        const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
+        float* pt = slot + t * kPartTile;
+        const float l_tot = exchange(l_sum[t], false);
+        if (half == 0) { pt[kBM * kD + row] = m_used[t]; pt[kBM * kD + kBM + row] = l_tot; }
+#pragma unroll
+        for (int c = 0; c < 64; c += 32) {
+          uint32_t r[32];
+          tmem_ld32(t_o + c0 + c, r);
+          tmem_wait_ld32(r);
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<uint4*>(pt + (((c0 + c + i) >> 2) * kBM + row) * 4) =
+                make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);   // [col/4][row][4]: a warp stores 512 B runs
         }
       }
     }
   }
+  // pieces of this unit: ranges i_first.. that overlap key steps [a*n, (a+1)*n)
+  const int64_t u_lo = (int64_t)u.sk_unit * n_main, u_hi = u_lo + n_main;
+  const int64_t total = (int64_t)p.sk_units * n_main;
+  const int i_first = (int)((u_lo * p.sk_sms) / total);
+  int n_pieces = 0;
+  for (int i = max(0, i_first - 1); i < p.sk_sms; ++i) {
+    int64_t lo, hi;
+    sk_range(p, n_main, i, lo, hi);
+    if (lo >= u_hi) break;
+    if (hi > u_lo && hi > lo) ++n_pieces;
+  }
+  __threadfence();
+  softmax_bar_sync(1);
+  float* xflag = &sm.xchg[0][0][0][0];
+  if (threadIdx.x == 128) {                               // first softmax thread
+    const int ticket = atomicAdd(p.ws_count + u.sk_unit, 1);
+    xflag[0] = ticket == n_pieces - 1 ? 1.f : 0.f;
+  }
+  softmax_bar_sync(1);
+  if (xflag[0] == 0.f) return;
+  __threadfence();
+#pragma unroll 1
+  for (int t = 0; t < 2; ++t) {
+    if (t >= u.n_q) break;
+    const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+    // pass 1: the row max over the pieces
+    float m_all = -INFINITY;
+    for (int i = max(0, i_first - 1); i < p.sk_sms; ++i) {
+      int64_t lo, hi;
+      sk_range(p, n_main, i, lo, hi);
+      if (lo >= u_hi) break;
+      if (!(hi > u_lo && hi > lo)) continue;
+      const int k = (lo / n_main == u.sk_unit) ? 0 : 1;
+      const float* pt = p.ws_part + (size_t)(2 * i + k) * kPartFloats + t * kPartTile;
+      m_all = fmaxf(m_all, __ldcg(pt + kBM * kD + row));
+    }
+    // pass 2: O = sum_s O_s * 2^((m_s - m_all) * scale), l likewise; 32 columns at a time
+#pragma unroll 1
+    for (int c = 0; c < 64; c += 32) {
+      float acc[32], l_all = 0.f;
+#pragma unroll
+      for (int e = 0; e < 32; ++e) acc[e] = 0.f;
+      for (int i = max(0, i_first - 1); i < p.sk_sms; ++i) {
+        int64_t lo, hi;
+        sk_range(p, n_main, i, lo, hi);
+        if (lo >= u_hi) break;
+        if (!(hi > u_lo && hi > lo)) continue;
+        const int k = (lo / n_main == u.sk_unit) ? 0 : 1;
+        const float* pt = p.ws_part + (size_t)(2 * i + k) * kPartFloats + t * kPartTile;
+        const float f = ex2((__ldcg(pt + kBM * kD + row) - m_all) * scale);
+        l_all += f * __ldcg(pt + kBM * kD + kBM + row);
+#pragma unroll
+        for (int e = 0; e < 32; e += 4) {
+          const float4 o4 = __ldcg(reinterpret_cast<const float4*>(pt + (((c0 + c + e) >> 2) * kBM + row) * 4));
+          acc[e] += f * o4.x; acc[e + 1] += f * o4.y; acc[e + 2] += f * o4.z; acc[e + 3] += f * o4.w;
+        }
+      }
+      if (row < q_rows) store_out_row(p, b, h, q_row0 + row, acc, 1.f / l_all, c0 + c, 32);
+    }
+  }
+  if (threadIdx.x == 128) p.ws_count[u.sk_unit] = 0;      // ready for the next launch
 }
 
 // kMode 0: v1/v2 (one softmax warpgroup per tile), 1: v3 (two warpgroups, one tile at a time),
@@ -711,8 +866,9 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   extern __shared__ uint8_t smem_raw[];
   SmemV1& sm = *reinterpret_cast<SmemV1*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
-  const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const UnitV1 u = decode_unit(p, blockIdx.x);
+  if (u.n_local == 0) return;                       // empty stream-K piece (whole CTA, before any barrier)
+  const int bh = u.bh, b = bh / p.H, h = bh - b * p.H;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
@@ -787,20 +943,76 @@ static ca_status make_qkv_tmap(CUtensorMap* m, const void* base, int BH, int Nto
 }
 
 int g_attention_impl = 0;    // 0 = best available, 1 = force v0 (debug / A-B tests)
+int g_attention_streamk = 0; // 0 = auto (real SM count), -1 = never split, n > 0 = plan for n SMs (tests)
+
+// Stream-K plan for the main units of one launch.  W units of n key steps each on S SMs: the
+// first floor(W/S)*S run whole (one CTA each); the remaining R < S would leave S-R SMs idle for a
+// whole unit time, so their R*n key steps are cut into S equal ranges instead (each range touches
+// at most two units -> two CTAs per range, pieces of a unit merged by the last one to finish).
+struct SkPlan { int n_dp, sk_units, sk_sms; };
+
+static SkPlan plan_streamk(int W, int n_concept, int n_steps, bool allowed) {
+  SkPlan pl{W, 0, 0};
+  if (!allowed || g_attention_streamk < 0 || W == 0) return pl;
+  int S = g_attention_streamk;
+  if (S == 0) {
+    static int sm_count = 0;
+    if (sm_count == 0) {
+      int dev = 0;
+      if (cudaGetDevice(&dev) != cudaSuccess ||
+          cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+        return pl;
+    }
+    S = sm_count;
+  }
+  // the concept units (one CTA each, launched first) count towards the whole waves
+  const int whole = ((W + n_concept) / S) * S - n_concept;      // main units that run unsplit
+  const int R = whole >= 0 ? W - whole : W;
+  if (R <= 0 || R >= S) return pl;
+  // Splitting saves up to (1 - R/S) * n_steps key steps of wall time on the last wave.  It costs
+  // two extra CTA start-ups per SM, a 133 KB partial per piece and the merge (~10 key steps), and
+  // the two pieces of a range are separate CTAs placed by the hardware scheduler, so the last wave
+  // ends after about 1.5 range lengths, not 1.  Measured on B200 (scripts/bench_attention.py):
+  // R/S = 0.34 at 130 steps: 0.488 -> 0.394 ms; R/S = 0.35 (12 heads): 1.420 -> 1.391 ms;
+  // R/S = 0.70 at 130 steps: 2.780 -> 2.856 ms (worse); R/S = 0.76 at 34 steps: worse.
+  // Hence: split only when the tail wave is at most half full and the saving is >= 24 steps.
+  // In test mode (planned SM count given) only the structural limits apply.
+  const int64_t saved = (int64_t)(S - R) * n_steps / S;
+  if ((int64_t)R * n_steps / S < 4) return pl;
+  if (g_attention_streamk == 0 && (2 * R > S || saved < 24)) return pl;
+  pl.n_dp = W - R; pl.sk_units = R; pl.sk_sms = S;
+  return pl;
+}
+
+static bool impl_is_v3() {
+  return g_attention_impl == 0 || g_attention_impl == 4 || g_attention_impl == 5 || g_attention_impl == 10;
+}
 
 }  // namespace ca
 
 extern "C" void ca_debug_set_attention_impl(int impl) { ca::g_attention_impl = impl; }
+extern "C" void ca_debug_set_attention_streamk(int sms) { ca::g_attention_streamk = sms; }
 
-extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void* v, int B, int H,
-                                        int P, int T, int C, int mode, void* out_img,
-                                        void* out_txtc, void* stream) {
+extern "C" size_t ca_joint_attention_workspace_bytes(int B, int H, int P, int T, int C, int mode) {
+  using namespace ca;
+  if (B <= 0 || H <= 0 || P + T <= 0 || !impl_is_v3()) return 0;
+  const int n_main = (P + T + kBM - 1) / kBM;
+  const int n_concept = (C > 0 && mode != CA_ATTN_NEITHER) ? B * H : 0;
+  const SkPlan pl = plan_streamk(((n_main + 1) / 2) * B * H, n_concept, n_main, true);
+  if (pl.sk_sms == 0) return 0;
+  return (size_t)2 * pl.sk_sms * kPartFloats * sizeof(float) + (size_t)pl.sk_units * sizeof(int) + 256;
+}
+
+extern "C" ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v, int B, int H,
+                                           int P, int T, int C, int mode, void* out_img,
+                                           void* out_txtc, void* workspace, size_t workspace_bytes,
+                                           void* stream) {
   using namespace ca;
   if (!q || !k || !v || B < 0 || H <= 0 || P < 0 || T < 0 || C < 0) return CA_ERR_INVALID_ARG;
   if (mode < CA_ATTN_BOTH || mode > CA_ATTN_NEITHER) return CA_ERR_INVALID_ARG;
   if (C > CA_MAX_CONCEPTS) return CA_ERR_UNSUPPORTED;
   if ((P > 0 && !out_img) || (T + C > 0 && !out_txtc)) return CA_ERR_INVALID_ARG;
-  const void* ptrs[] = {q, k, v, out_img, out_txtc};
+  const void* ptrs[] = {q, k, v, out_img, out_txtc, workspace};
   for (const void* ptr : ptrs) if (ptr && !aligned16(ptr)) return CA_ERR_ALIGNMENT;
   const int Ntot = P + T + C;
   if (B == 0 || Ntot == 0) return CA_OK;
@@ -813,6 +1025,8 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
   p.out_img = (__nv_bfloat16*)out_img;
   p.out_txtc = (__nv_bfloat16*)out_txtc;
   p.scale_log2 = kLog2e / sqrtf((float)kD);
+  p.n_pairs = (p.n_main_tiles + 1) / 2;
+  p.ws_part = nullptr; p.ws_count = nullptr;
 
   CUtensorMap tmq, tmk, tmv;
   ca_status s;
@@ -830,8 +1044,20 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
       CA_LAUNCH_CHECK();
     }
   } else {
-    const int units = (p.n_main_tiles + 1) / 2 + (concept_attn ? 1 : 0);
-    if (units > 0) {
+    const int W = p.n_pairs * B * H;
+    const size_t need = ca_joint_attention_workspace_bytes(B, H, P, T, C, mode);
+    p.n_concept = concept_attn ? B * H : 0;
+    const SkPlan pl = plan_streamk(W, p.n_concept, p.n_main_tiles,
+                                   impl_is_v3() && workspace != nullptr && need > 0 && workspace_bytes >= need);
+    p.n_dp = pl.n_dp; p.sk_units = pl.sk_units; p.sk_sms = pl.sk_sms;
+    if (pl.sk_sms > 0) {
+      p.ws_part = (float*)workspace;
+      p.ws_count = (int*)((char*)workspace + (size_t)2 * pl.sk_sms * kPartFloats * sizeof(float));
+      CA_CUDA_OK(cudaMemsetAsync(p.ws_count, 0, (size_t)pl.sk_units * sizeof(int), st));
+    }
+    const int64_t ctas = (int64_t)p.n_dp + 2 * p.sk_sms + p.n_concept;
+    if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
+    if (ctas > 0) {
       const int smem = (int)sizeof(SmemV1) + 1024;
       // impl 0: v3 (two cooperating warpgroups), polynomial exp2 on every 4th element pair;
       // 4 / 5: v3 every 2nd pair / all MUFU; 2 / 3: v2 (one warpgroup per tile) all MUFU / every 4th;
@@ -848,7 +1074,7 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
                 : g_attention_impl == 7 ? attn_v1_kernel<0, 2> : attn_v1_kernel<4, 1>;
       const bool v4 = g_attention_impl == 9 || g_attention_impl == 6 || g_attention_impl == 7;
       CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      kern<<<dim3(units, B * H), v4 ? 640 : 384, smem, st>>>(tmq, tmk, tmv, p);
+      kern<<<(unsigned)ctas, v4 ? 640 : 384, smem, st>>>(tmq, tmk, tmv, p);
       CA_LAUNCH_CHECK();
     }
   }
@@ -858,4 +1084,10 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
     CA_LAUNCH_CHECK();
   }
   return CA_OK;
+}
+
+extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void* v, int B, int H,
+                                        int P, int T, int C, int mode, void* out_img,
+                                        void* out_txtc, void* stream) {
+  return ca_joint_attention_ws(q, k, v, B, H, P, T, C, mode, out_img, out_txtc, nullptr, 0, stream);
 }

@@ -127,14 +127,18 @@ def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_tx
         out_img = torch.empty(B, P, H * 128, device=q.device, dtype=BF16)
     if out_txtc is None:
         out_txtc = torch.empty(B, T + C, H * 128, device=q.device, dtype=BF16)
+    lib = _cabi.load()
+    # scratch for the stream-K tail (0 bytes when this shape is never split); torch owns it
+    ws_bytes = lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, mode)
+    ws = torch.empty(ws_bytes, device=q.device, dtype=torch.uint8) if ws_bytes else None
     ev = None
     if ATTN_EVENTS is not None:
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
         ev[0].record()
-    check(_cabi.load().ca_joint_attention(
+    check(lib.ca_joint_attention_ws(
         q.data_ptr(), k.data_ptr(), v.data_ptr(), B, H, P, T, C, mode,
         out_img.data_ptr() if P > 0 else None, out_txtc.data_ptr() if T + C > 0 else None,
-        _stream(q)), "ca_joint_attention")
+        ws.data_ptr() if ws is not None else None, ws_bytes, _stream(q)), "ca_joint_attention_ws")
     if ev is not None:
         ev[1].record()
         ATTN_EVENTS.append((ev, B, P, T, C, H))

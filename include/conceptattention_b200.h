@@ -107,6 +107,19 @@ ca_status ca_joint_attention(const void* q, const void* k, const void* v,
                              int B, int H, int P, int T, int C, int mode,
                              void* out_img, void* out_txtc, void* stream);
 
+/* Same, with a caller-owned scratch buffer that lets the launch balance its last wave:
+ * when the query-tile units do not fill a whole number of waves of the GPU's SMs, the key
+ * range of the left-over units is cut into one equal share per SM (stream-K) and the pieces
+ * of a unit are merged in fp32 by whichever piece finishes last (fixed merge order: results
+ * do not depend on timing).  `workspace` needs ca_joint_attention_workspace_bytes(...) bytes
+ * (0 = this shape is never split), 16-byte aligned, contents irrelevant; with a null or too
+ * small workspace the call behaves exactly like ca_joint_attention. */
+size_t ca_joint_attention_workspace_bytes(int B, int H, int P, int T, int C, int mode);
+ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v,
+                                int B, int H, int P, int T, int C, int mode,
+                                void* out_img, void* out_txtc,
+                                void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- K3+K4: heatmap logits + normalise over concepts + accumulate -----------
  * logits[b,c,p] = sum_{s<nseg} sum_{j<seg_len} img[b,s,p,j] * con[b,s,c,j]
  * where element (b,s,p,j) sits at img + b*img_stride_b + s*img_stride_s +

@@ -19,6 +19,8 @@ SHAPES = [  # name, B, H, P, T, C
     ("cfg3 512^2 batch 16", 16, 24, 1024, 256, 2),
     ("cfg4 dev 1024^2 C=20", 1, 24, 4096, 512, 20),
     ("cfg5 2048^2 C=32", 1, 24, 16384, 256, 32),
+    ("cfg5 head-sharded over 8 GPUs (3 heads)", 1, 3, 16384, 256, 32),
+    ("cfg5 head-sharded over 2 GPUs (12 heads)", 1, 12, 16384, 256, 32),
 ]
 
 
@@ -31,6 +33,8 @@ def main():
     pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
     lib = _cabi.load()
+    # CA_STREAMK=-1: never split the last wave (A/B against the default plan)
+    lib.ca_debug_set_attention_streamk(int(os.environ.get("CA_STREAMK", "0")))
     for name, B, H, P, T, C in SHAPES:
         if args.only not in name:
             continue

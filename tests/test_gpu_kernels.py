@@ -176,6 +176,36 @@ def test_joint_attention(ops, B, H, P, T, C, mode):
     close(ot, rt, rtol=2e-2, atol=1e-2)
 
 
+@pytest.mark.parametrize("B,H,P,T,C,sms", [(1, 2, 2000, 200, 3, 7), (1, 2, 2200, 200, 3, 6), (1, 2, 2200, 200, 0, 6),
+                                           (1, 2, 2200, 200, 5, 24), (2, 3, 1100, 100, 2, 8)])
+def test_joint_attention_stream_k_tail(ops, B, H, P, T, C, sms):
+    """Stream-K tail: with the plan made for `sms` SMs the left-over query-tile units are cut
+    by KEY range into one share per SM and merged by the last piece to finish.  The result
+    must match the oracle like the unsplit launch does, be (near-)identical to the unsplit
+    launch (fp32 merge vs in-TMEM accumulation: one bf16 ulp), and be REPRODUCIBLE — the
+    merge order is fixed, so repeated launches are bit-identical whatever finishes last."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    N = P + T + C
+    q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((30, 1.5), (31, 1.0), (32, 1.0)))
+    try:
+        lib.ca_debug_set_attention_streamk(-1)
+        assert lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, 0) == 0
+        base = ops.joint_attention(q, k, v, P, T, C)
+        lib.ca_debug_set_attention_streamk(sms)
+        assert lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, 0) > 0, "plan did not split: pick other sizes"
+        runs = [ops.joint_attention(q, k, v, P, T, C) for _ in range(3)]
+        torch.cuda.synchronize()
+    finally:
+        lib.ca_debug_set_attention_streamk(0)
+    ri, rt = _attention_oracle(q.float().cpu(), k.float().cpu(), v.float().cpu(), P, T, C, 0)
+    for got, ref, b in zip(runs[0], (ri, rt), base):
+        close(got, ref, rtol=2e-2, atol=1e-2)
+        close(got, b, rtol=8e-3, atol=2e-3)
+    for r in runs[1:]:
+        assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1])
+
+
 def test_joint_attention_one_way(ops):
     """Image and text rows must not depend on the concept tokens at all (bit-exact)."""
     B, H, P, T, C = 1, 2, 384, 128, 5
