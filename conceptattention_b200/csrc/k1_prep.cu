@@ -161,10 +161,12 @@ ln_stream_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t row_bytes = (uint32_t)D * 2u;
   const uint32_t slot_bytes = row_bytes * (kResidual ? 2u : 1u);
-  // layout: [a1 fp32 D | sh fp32 D] (only with an output) | row slots | mbarriers
+  // layout: [a1 fp32 D | sh fp32 D] (only with an output) | [gate bf16 D] (residual forms) |
+  //         row slots | mbarriers
   float* a1_s = reinterpret_cast<float*>(smem);
   float* sh_s = a1_s + D;
-  uint8_t* slots_base = smem + (out != nullptr ? (size_t)D * 8 : 0);
+  uint8_t* gate_s = smem + (out != nullptr ? (size_t)D * 8 : 0);
+  uint8_t* slots_base = gate_s + (kResidual ? (size_t)D * 2 : 0);
   uint8_t* wbase = slots_base + (size_t)warp * slots * slot_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(slots_base + (size_t)kStreamWarps * slots * slot_bytes) + warp * slots;
   const int64_t r_begin = (int64_t)blockIdx.x * rows / gridDim.x;
@@ -189,19 +191,23 @@ ln_stream_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict_
   // one modulation row for the whole CTA?  (first and last row in the same batch element and
   // on the same side of `split`)
   bool cached = false;
-  if (out != nullptr && r_end > r_begin) {
+  if (r_end > r_begin) {
     const int b0 = (int)(r_begin / N), b1 = (int)((r_end - 1) / N);
     const int n0 = (int)(r_begin - (int64_t)b0 * N), n1 = (int)(r_end - 1 - (int64_t)b1 * N);
     cached = b0 == b1 && (n0 < split) == (n1 < split);
     if (cached) {
       const __nv_bfloat16* mod = (n0 < split ? mod0 : mod1) + (int64_t)b0 * mod_stride;
       for (int c = threadIdx.x; c < nchunks; c += blockDim.x) {
-        uint64_t a1[4], sh[4];
-        mod_chunk_global(mod, shift_off, scale_off, c, a1, sh);
+        if (kResidual)
+          reinterpret_cast<uint4*>(gate_s)[c] = *reinterpret_cast<const uint4*>(mod + gate_off + c * 8);
+        if (out != nullptr) {
+          uint64_t a1[4], sh[4];
+          mod_chunk_global(mod, shift_off, scale_off, c, a1, sh);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          reinterpret_cast<uint64_t*>(a1_s)[c * 4 + j] = a1[j];
-          reinterpret_cast<uint64_t*>(sh_s)[c * 4 + j] = sh[j];
+          for (int j = 0; j < 4; ++j) {
+            reinterpret_cast<uint64_t*>(a1_s)[c * 4 + j] = a1[j];
+            reinterpret_cast<uint64_t*>(sh_s)[c * 4 + j] = sh[j];
+          }
         }
       }
     }
@@ -223,9 +229,10 @@ ln_stream_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict_
       if (c < nchunks) {
         unpack8_pairs(*reinterpret_cast<const uint4*>(src + c * 16), v[k]);
         if (kResidual) {
+          const uint4 graw = cached ? reinterpret_cast<const uint4*>(gate_s)[c]
+                                    : *reinterpret_cast<const uint4*>(mod + gate_off + c * 8);
           *reinterpret_cast<uint4*>(x + row * D + c * 8) = residual_chunk(
-              v[k], *reinterpret_cast<const uint4*>(src + row_bytes + c * 16),
-              *reinterpret_cast<const uint4*>(mod + gate_off + c * 8));
+              v[k], *reinterpret_cast<const uint4*>(src + row_bytes + c * 16), graw);
         }
       } else {
 #pragma unroll
@@ -277,7 +284,8 @@ static ca_status launch_ln(void* x, const void* y, int64_t y_stride, void* out, 
   // Large token streams: persistent TMA-staged kernel, grid = SM count.  Small ones (the
   // text+concept rows) and rows too wide for the staging buffers keep the one-warp-per-row form.
   const size_t slot_bytes = (size_t)D * 2 * (kResidual ? 2 : 1);
-  const size_t cache_bytes = out ? (size_t)D * 8 : 0;             // fp32 (1+scale) and shift
+  // fp32 (1+scale) and shift (forms with an output) + bf16 gate (residual forms)
+  const size_t cache_bytes = (out ? (size_t)D * 8 : 0) + (kResidual ? (size_t)D * 2 : 0);
   const size_t budget = 226u * 1024u - cache_bytes;                // 227 KB per CTA on sm_100
   const int slots = (int)std::min<size_t>(2, budget / (kStreamWarps * (slot_bytes + 8) + 256));
   // Measured on B200 (scripts/bench_k1.py): the plain LN (one input stream) is faster in the
