@@ -177,6 +177,8 @@ def run_ours(args, rank, world, local_rank):
             return out.concept_heatmaps, out.cross_attention_maps
 
     gen.model.use_graphs = not args.no_graphs
+    if args.no_side_stream:
+        gen.model.use_side_stream = False
     for i in range(args.warmup):
         device_step(i)
     barrier()
@@ -370,6 +372,7 @@ def main():
     ap.add_argument("--config", default="schnell-1024", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel individually (A/B)")
+    ap.add_argument("--no-side-stream", action="store_true", help="text stream on the main CUDA stream (A/B)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

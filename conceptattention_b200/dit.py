@@ -210,6 +210,12 @@ class FluxDiTEngine:
         # CUDA graphs of whole forwards (one per signature), captured the second time a
         # signature is seen; the first call runs launch by launch and warms cuBLAS.
         self.use_graphs = True
+        # the text+concept stream of a double block (five small, latency-bound launches per
+        # GEMM pair) runs on a second CUDA stream beside the image stream; captured graphs keep
+        # the fork/join as parallel branches.  Off in the head-sharded mode (one NCCL
+        # communicator must see its collectives from one stream).
+        self.use_side_stream = head_shard is None or head_shard.world == 1
+        self._side = None
         self.max_graphs = 8
         self._graphs, self._graph_seen, self._graph_pool = {}, {}, None
 
@@ -386,12 +392,35 @@ class FluxDiTEngine:
         o_i, o_t = off("double_blocks.0.img_mod.lin"), off("double_blocks.0.txt_mod.lin")
         ln = {"img": ops.ln_modulate(x_img, m_vec, None, None, o_i, o_i + D),
               "txt": ops.ln_modulate(txtc, m_vec, m_con, T, o_t, o_t + D)}
+        side = None
+        if self.use_side_stream and not sharded:
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=dev)
+            side = self._side
+        main = torch.cuda.current_stream(dev)
+
+        def txt_chain(i, attn_tc):
+            """proj -> gated residual + LN -> MLP -> gated residual (+ next block's LN) -> next
+            block's qkv GEMM, all on the text+concept rows; returns the next tc_qkv (or None)."""
+            pre = f"double_blocks.{i}"
+            o = off(pre + ".txt_mod.lin")
+            proj = self._lin_rp(pre + ".txt_attn.proj", attn_tc)
+            h = ops.gate_residual_ln_modulate(txtc, proj, m_vec, m_con, T, o + 2 * D, o + 3 * D, o + 4 * D)
+            h = self._lin_rp(pre + ".txt_mlp.2", self._lin_gelu(pre + ".txt_mlp.0", h))
+            if i + 1 < p.depth:
+                on = off(f"double_blocks.{i + 1}.txt_mod.lin")
+                ln_t = ops.gate_residual_ln_modulate(txtc, h, m_vec, m_con, T, o + 5 * D, on, on + D)
+                return self._lin(f"double_blocks.{i + 1}.txt_attn.qkv", ln_t)
+            ops.gate_residual_ln_modulate(txtc, h, m_vec, m_con, T, o + 5 * D, 0, 0, want_out=False)
+            return None
+
+        tc_qkv = self._lin("double_blocks.0.txt_attn.qkv", ln.pop("txt")) if p.depth else None
         for i in range(p.depth):
             pre = f"double_blocks.{i}"
             sel = collect_vectors or (accumulator is not None and accumulator.multiplicity(i) > 0)
-            # qkv GEMMs (concept rows ride on the txt GEMM)
             img_qkv = self._lin(pre + ".img_attn.qkv", ln["img"])
-            tc_qkv = self._lin(pre + ".txt_attn.qkv", ln["txt"])
+            if side is not None and i > 0:
+                main.wait_stream(side)                   # join: tc_qkv (and txtc) of the side branch
             res = ops.qkv_prep(
                 img_qkv, tc_qkv,
                 (self.sd[pre + ".img_attn.norm.query_norm.scale"], self.sd[pre + ".img_attn.norm.key_norm.scale"]),
@@ -417,17 +446,28 @@ class FluxDiTEngine:
                 collected["output_space_image_vectors"].append(gather(attn_img))
                 collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
                 collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
-            # residual updates; concept rows use the txt weights with their own gates
-            for x, attn, m1, split, s in ((x_img, attn_img, None, None, "img"), (txtc, attn_tc, m_con, T, "txt")):
-                o = off(f"{pre}.{s}_mod.lin")
-                proj = self._lin_rp(f"{pre}.{s}_attn.proj", attn)
-                h = ops.gate_residual_ln_modulate(x, proj, m_vec, m1, split, o + 2 * D, o + 3 * D, o + 4 * D)
-                h = self._lin_rp(f"{pre}.{s}_mlp.2", self._lin_gelu(f"{pre}.{s}_mlp.0", h))
-                if i + 1 < p.depth:
-                    on = off(f"double_blocks.{i + 1}.{s}_mod.lin")
-                    ln[s] = ops.gate_residual_ln_modulate(x, h, m_vec, m1, split, o + 5 * D, on, on + D)
-                else:
-                    ops.gate_residual_ln_modulate(x, h, m_vec, m1, split, o + 5 * D, 0, 0, want_out=False)
+            # residual updates.  Text+concept rows (txt weights, per-segment gates) fork onto the
+            # side stream right after the attention; the image rows stay on the main stream.  The
+            # side branch runs on into the next block's txt qkv GEMM and is joined before K1b.
+            if side is not None:
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    tc_qkv = txt_chain(i, attn_tc)
+                # (no record_stream needed: every tensor the branch reads outlives the join at the
+                # next block's K1b, and everything it allocates is first reused after a later fork)
+            else:
+                tc_qkv = txt_chain(i, attn_tc)
+            o = off(pre + ".img_mod.lin")
+            proj = self._lin_rp(pre + ".img_attn.proj", attn_img)
+            h = ops.gate_residual_ln_modulate(x_img, proj, m_vec, None, None, o + 2 * D, o + 3 * D, o + 4 * D)
+            h = self._lin_rp(pre + ".img_mlp.2", self._lin_gelu(pre + ".img_mlp.0", h))
+            if i + 1 < p.depth:
+                on = off(f"double_blocks.{i + 1}.img_mod.lin")
+                ln["img"] = ops.gate_residual_ln_modulate(x_img, h, m_vec, None, None, o + 5 * D, on, on + D)
+            else:
+                ops.gate_residual_ln_modulate(x_img, h, m_vec, None, None, o + 5 * D, 0, 0, want_out=False)
+        if side is not None and p.depth:
+            main.wait_stream(side)                       # txtc is final
         if collect_vectors:
             collected = {k: torch.stack(v, 0) for k, v in collected.items()}
         else:

@@ -253,3 +253,29 @@ def test_graph_replay_equals_launch_by_launch():
     got_e = [enc(l) for l in lat]
     for a, b in zip(got_e, ref_e):
         np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7)
+
+
+def test_side_stream_equals_single_stream():
+    """Running the text+concept chain of the double blocks on a second stream (eagerly and
+    inside captured graphs) changes scheduling only: heatmaps and prediction are bit-identical
+    to the single-stream run."""
+    from conceptattention_b200 import ConceptAttentionFluxPipeline
+    pipe = ConceptAttentionFluxPipeline(model_name="tiny", device="cuda:0")
+    eng = pipe.flux_generator.model
+    kw = dict(width=256, height=256, layer_indices=[0, 2], num_inference_steps=3,
+              return_pil_heatmaps=False, decode_image=True)
+
+    def run(seed):
+        o = pipe.generate_image("a dragon on a rock", ["dragon", "rock", "sky"], seed=seed, **kw)
+        return np.stack([o.concept_heatmaps, o.cross_attention_maps]), np.asarray(o.image)
+
+    out = {}
+    for side in (False, True):
+        for graphs in (False, True):
+            eng.use_side_stream, eng.use_graphs = side, graphs
+            eng._graphs.clear(); eng._graph_seen.clear()
+            out[(side, graphs)] = [run(s) for s in (0, 1)]
+    ref = out[(False, False)]
+    for key, got in out.items():
+        for (h, img), (h0, img0) in zip(got, ref):
+            assert np.array_equal(h, h0) and np.array_equal(img, img0), key
