@@ -215,6 +215,7 @@ class FluxDiTEngine:
         # the fork/join as parallel branches.  Off in the head-sharded mode (one NCCL
         # communicator must see its collectives from one stream).
         self.use_side_stream = head_shard is None or head_shard.world == 1
+        self.skip_unused_tail = True      # see the double-block loop (encode path only)
         self._side = None
         self.max_graphs = 8
         self._graphs, self._graph_seen, self._graph_pool = {}, {}, None
@@ -446,6 +447,14 @@ class FluxDiTEngine:
                 collected["output_space_image_vectors"].append(gather(attn_img))
                 collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
                 collected["cross_attention_image_vectors"].append(q_pre[:, :, :P].clone())
+            # encode_image path (stop_after_multimodal_attentions, heatmaps only): nothing after
+            # the last selected layer's attention is ever read — the reference still runs those
+            # proj/MLP updates (and whole blocks) and discards them
+            # (modified_flux_dit.py:147-153); here they are not computed.
+            if (self.skip_unused_tail and stop_after_multimodal_attentions and not collect_vectors
+                    and accumulator is not None
+                    and not any(accumulator.multiplicity(l) > 0 for l in range(i + 1, p.depth))):
+                break
             # residual updates.  Text+concept rows (txt weights, per-segment gates) fork onto the
             # side stream right after the attention; the image rows stay on the main stream.  The
             # side branch runs on into the next block's txt qkv GEMM and is joined before K1b.

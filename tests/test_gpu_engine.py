@@ -279,3 +279,28 @@ def test_side_stream_equals_single_stream():
     for key, got in out.items():
         for (h, img), (h0, img0) in zip(got, ref):
             assert np.array_equal(h, h0) and np.array_equal(img, img0), key
+
+
+def test_encode_skips_dead_tail_without_changing_heatmaps():
+    """encode_image never reads anything after the last selected layer's attention; not
+    computing it (the reference does, then discards it) leaves the heatmaps bit-identical."""
+    from conceptattention_b200 import ConceptAttentionFluxPipeline, ops
+    pipe = ConceptAttentionFluxPipeline(model_name="tiny", device="cuda:0")
+    eng = pipe.flux_generator.model
+    eng.use_graphs = False
+    lat = torch.randn(2, 16, 32, 32, generator=torch.Generator().manual_seed(5))
+    res = {}
+    for skip in (False, True):
+        eng.skip_unused_tail = skip
+        for layers in ([0, 2], [0, 1]):
+            n0 = ops.LAUNCHES
+            o = pipe.encode_image(lat, ["dragon", "sky"], width=256, height=256, layer_indices=layers,
+                                  return_pil_heatmaps=False)
+            res[(skip, tuple(layers))] = (np.stack([o.concept_heatmaps, o.cross_attention_maps]),
+                                          ops.LAUNCHES - n0)
+    for layers in ((0, 2), (0, 1)):
+        full, n_full = res[(False, layers)]
+        cut, n_cut = res[(True, layers)]
+        assert np.array_equal(full, cut)
+        assert n_cut < n_full
+    assert res[(True, (0, 1))][1] < res[(True, (0, 2))][1]      # a whole block less
