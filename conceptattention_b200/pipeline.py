@@ -12,6 +12,7 @@ dict is supplied, and the text encoders are `SyntheticEmbedder`s.
 from __future__ import annotations
 
 import math
+import os
 import time
 from dataclasses import dataclass
 
@@ -20,7 +21,7 @@ import torch
 
 from . import _cabi, ops, sampling
 from .dit import FluxDiTEngine, HeatmapAccumulator
-from .weights import CONFIGS, T5_MAX_LENGTH, init_state_dict
+from .weights import CONFIGS, T5_MAX_LENGTH, init_state_dict, load_checkpoint
 
 try:                                     # PIL is optional at import time
     import PIL.Image
@@ -75,6 +76,8 @@ class FluxGenerator:
         self.model_name = model_name
         self.is_schnell = "schnell" in model_name or model_name == "tiny"
         self.params = CONFIGS[model_name]
+        if isinstance(state_dict, (str, os.PathLike)):       # a flux1-*.safetensors / .pt file
+            state_dict = load_checkpoint(state_dict, self.params, device=self.device)
         if state_dict is None:
             state_dict = init_state_dict(self.params, seed=seed, device=self.device,
                                          dtype=torch.bfloat16)

@@ -14,7 +14,8 @@ from dataclasses import asdict, dataclass, field
 
 import torch
 
-__all__ = ["FluxParams", "CONFIGS", "T5_MAX_LENGTH", "linear_shapes", "init_state_dict"]
+__all__ = ["FluxParams", "CONFIGS", "T5_MAX_LENGTH", "linear_shapes", "init_state_dict",
+           "expected_keys", "load_checkpoint"]
 
 
 @dataclass
@@ -116,4 +117,50 @@ def init_state_dict(p: FluxParams, seed: int = 0, device="cpu", dtype=torch.floa
         if norm_scale_jitter:
             s = s + norm_scale_jitter * (torch.rand(d, generator=g, device=device) * 2 - 1)
         sd[k] = s.to(dtype)
+    return sd
+
+
+def expected_keys(p: FluxParams) -> dict:
+    """{state-dict key: shape} of ModifiedFluxDiT for `p` (what a flux1-*.safetensors holds)."""
+    shapes = {}
+    for name, (out_f, in_f) in linear_shapes(p).items():
+        shapes[name + ".weight"] = (out_f, in_f)
+        if p.qkv_bias or not name.endswith("_attn.qkv"):
+            shapes[name + ".bias"] = (out_f,)
+    d = p.hidden_size // p.num_heads
+    for i in range(p.depth):
+        for st in ("img", "txt"):
+            for qk in ("query", "key"):
+                shapes[f"double_blocks.{i}.{st}_attn.norm.{qk}_norm.scale"] = (d,)
+    for i in range(p.depth_single_blocks):
+        for qk in ("query", "key"):
+            shapes[f"single_blocks.{i}.norm.{qk}_norm.scale"] = (d,)
+    return shapes
+
+
+def load_checkpoint(path: str, p: FluxParams, device="cpu", dtype=torch.bfloat16, strict=True) -> dict:
+    """Read a Flux checkpoint with the reference's key names — the file
+    `load_flow_model` feeds to `model.load_state_dict` (concept_attention/image_generator.py:19-48): `.safetensors` (tensors are read one by one straight to
+    `device`) or a torch `.pt/.pth` state dict.  Keys and shapes are checked against
+    `expected_keys(p)`; `strict=False` tolerates extra keys (e.g. the reference's
+    non-persistent buffers) but never missing or mis-shaped ones."""
+    want = expected_keys(p)
+    sd = {}
+    if str(path).endswith(".safetensors"):
+        from safetensors import safe_open
+        with safe_open(str(path), framework="pt", device=str(device)) as f:
+            names = list(f.keys())
+            for k in names:
+                if k in want:
+                    sd[k] = f.get_tensor(k).to(dtype)
+    else:
+        raw = torch.load(str(path), map_location=device, weights_only=True)
+        names = list(raw.keys())
+        sd = {k: v.to(dtype) for k, v in raw.items() if k in want}
+    missing = sorted(set(want) - set(sd))
+    extra = sorted(set(names) - set(want))
+    bad = sorted(k for k, v in sd.items() if tuple(v.shape) != tuple(want[k]))
+    if missing or bad or (strict and extra):
+        raise ValueError(f"checkpoint does not match {type(p).__name__}: missing={missing[:5]} "
+                         f"({len(missing)}), wrong shape={bad[:5]} ({len(bad)}), unexpected={extra[:5]} ({len(extra)})")
     return sd
