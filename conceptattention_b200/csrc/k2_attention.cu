@@ -635,7 +635,13 @@ __device__ __forceinline__ void softmax_bar_sync(int id) {
 // two warpgroups) owns the other tile and runs concurrently, staggered by the MMA pipeline, so
 // each SM sub-partition holds four softmax warps in two different phases: one pair's
 // TMEM-load / max / exchange / pack / TMEM-store latency hides under the other's MUFU stream.
-template <int kPolyEvery, int kTile>
+// kOpt (optimistic max): after the first key tile the exp2 stream starts at once with the row
+// max already in use and the exchange of this tile's max moves behind it (same single barrier
+// per tile, which still orders every S read before any P write).  Only when the exchanged max
+// turns out to exceed the one in use by more than the lazy-rescale threshold — rare after the
+// first tiles — is the tile redone from the S values still in registers, exactly as the plain
+// path would have done it: results are bit-identical.
+template <int kPolyEvery, int kTile, bool kOpt = false>
 __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const UnitV1& u,
                                            const AttnParams& p, int half, int b, int h) {
   constexpr int kPair = kTile < 0 ? 0 : kTile;
@@ -686,30 +692,11 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
         tmem_wait_ld32(rb);
         mask_chunk(ra, c0, valid);
         mask_chunk(rb, c0 + 32, valid);
-        const float mx = exchange(max_chunk(rb, max_chunk(ra, -INFINITY)), true);
-        const bool grow = (mx - m_used[t]) * scale > kRescaleThreshold;   // true on the first tile
-        const float m_new = grow ? mx : m_used[t];
-        if (j > 0 && __any_sync(0xffffffffu, grow)) {
-          // PV_t(j-1) has completed: the commit behind s_full[t] covers it.
-          const float alpha = grow ? ex2((m_used[t] - m_new) * scale) : 1.f;
-          l_sum[t] *= alpha;
-          // rare path: 8 columns at a time so it adds nothing to the loop's register budget
-#pragma unroll 1
-          for (int c = 0; c < 64; c += 8) {
-            uint32_t rc[8];
-            tmem_ld8(t_o + c0 + c, rc);
-            tmem_wait_ld8(rc);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
-            tmem_st8(t_o + c0 + c, rc);
-          }
-        }
-        m_used[t] = m_new;
-        const float mb = m_new * scale;
-        const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
-        uint64_t rs2 = pk64(0.f, 0.f);
-        auto exp_chunk = [&](const uint32_t* r, int pcol) {
-          uint32_t pk[16];
+        const float m_loc = max_chunk(rb, max_chunk(ra, -INFINITY));
+        // P = exp2(S * scale - m * scale) for one 32-column chunk -> 16 packed bf16 pairs
+        auto exp_regs = [&](const uint32_t* r, float m_ref, uint32_t* pk, uint64_t& rs2) {
+          const float mb = m_ref * scale;
+          const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const uint64_t x2 = fma2(pk64(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), scale2, nmb2);
@@ -724,10 +711,56 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
             rs2 = add2(rs2, pk64(e0, e1));
             pk[i] = pack2(e0, e1);
           }
-          tmem_st16(t_s + pcol, pk);                      // P_t over S_t columns [0,64)
         };
-        exp_chunk(ra, half * 32);
-        exp_chunk(rb, half * 32 + 16);
+        auto rescale_o = [&](float alpha) {
+          // rare path: 8 columns at a time so it adds nothing to the loop's register budget
+#pragma unroll 1
+          for (int c = 0; c < 64; c += 8) {
+            uint32_t rc[8];
+            tmem_ld8(t_o + c0 + c, rc);
+            tmem_wait_ld8(rc);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+            tmem_st8(t_o + c0 + c, rc);
+          }
+        };
+        uint32_t pka[16], pkb[16];
+        uint64_t rs2 = pk64(0.f, 0.f);
+        if (kOpt && j > 0) {
+          float* xb = &sm.xchg[kPair][use & 1][0][0];
+          xb[half * kBM + row] = m_loc;
+          exp_regs(ra, m_used[t], pka, rs2);              // optimistic: the max in use still holds
+          exp_regs(rb, m_used[t], pkb, rs2);
+          softmax_bar_sync(1 + kPair);
+          const float mx = fmaxf(m_loc, xb[(half ^ 1) * kBM + row]);
+          ++use;
+          const bool grow = (mx - m_used[t]) * scale > kRescaleThreshold;
+          if (__any_sync(0xffffffffu, grow)) {            // rare: redo the tile with the new max
+            const float m_new = grow ? mx : m_used[t];
+            const float alpha = grow ? ex2((m_used[t] - m_new) * scale) : 1.f;
+            l_sum[t] *= alpha;
+            rescale_o(alpha);                             // PV_t(j-1) is complete (see s_full)
+            m_used[t] = m_new;
+            rs2 = pk64(0.f, 0.f);
+            exp_regs(ra, m_new, pka, rs2);
+            exp_regs(rb, m_new, pkb, rs2);
+          }
+        } else {
+          const float mx = exchange(m_loc, true);
+          const bool grow = (mx - m_used[t]) * scale > kRescaleThreshold;   // true on the first tile
+          const float m_new = grow ? mx : m_used[t];
+          if (j > 0 && __any_sync(0xffffffffu, grow)) {
+            // PV_t(j-1) has completed: the commit behind s_full[t] covers it.
+            const float alpha = grow ? ex2((m_used[t] - m_new) * scale) : 1.f;
+            l_sum[t] *= alpha;
+            rescale_o(alpha);
+          }
+          m_used[t] = m_new;
+          exp_regs(ra, m_new, pka, rs2);
+          exp_regs(rb, m_new, pkb, rs2);
+        }
+        tmem_st16(t_s + half * 32, pka);                  // P_t over S_t columns [0,64)
+        tmem_st16(t_s + half * 32 + 16, pkb);
         float r0, r1;
         upk64(rs2, r0, r1);
         l_sum[t] += r0 + r1;
@@ -859,6 +892,7 @@ __device__ __forceinline__ void v3_softmax(SmemV1& sm, uint32_t tmem, const Unit
 // kMode 0: v1/v2 (one softmax warpgroup per tile), 1: v3 (two warpgroups, one tile at a time),
 // 2: v4 (four warpgroups = two column-half pairs, one pair per tile, 640 threads; MMA issue loops
 // rolled — unrolled they spill at 32 registers and measured 5-20 % slower).
+// 3: v3 with the optimistic row max (see v3_softmax).
 template <int kPolyEvery, int kMode>
 __global__ void __launch_bounds__(kMode == 2 ? 640 : 384, 1)
 attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
@@ -902,6 +936,7 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
     setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
     if (kMode == 1) v3_softmax<kPolyEvery, -1>(sm, tmem, u, p, t, b, h);
+    else if (kMode == 3) v3_softmax<kPolyEvery, -1, true>(sm, tmem, u, p, t, b, h);
     else if (t < u.n_q) v1_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
   }
   tc_fence_before();
@@ -985,7 +1020,8 @@ static SkPlan plan_streamk(int W, int n_concept, int n_steps, bool allowed) {
 }
 
 static bool impl_is_v3() {
-  return g_attention_impl == 0 || g_attention_impl == 4 || g_attention_impl == 5 || g_attention_impl == 10;
+  return g_attention_impl == 0 || g_attention_impl == 4 || g_attention_impl == 5 || g_attention_impl == 10 ||
+         g_attention_impl == 13;
 }
 
 }  // namespace ca
@@ -1070,6 +1106,7 @@ extern "C" ca_status ca_joint_attention_ws(const void* q, const void* k, const v
                 : g_attention_impl == 5 ? attn_v1_kernel<0, 1>
                 : g_attention_impl == 9 ? attn_v1_kernel<4, 2>
                 : g_attention_impl == 10 ? attn_v1_kernel<-3, 1>
+                : g_attention_impl == 13 ? attn_v1_kernel<4, 3>
                 : g_attention_impl == 6 ? attn_v1_kernel<2, 2>
                 : g_attention_impl == 7 ? attn_v1_kernel<0, 2> : attn_v1_kernel<4, 1>;
       const bool v4 = g_attention_impl == 9 || g_attention_impl == 6 || g_attention_impl == 7;

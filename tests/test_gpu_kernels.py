@@ -206,6 +206,32 @@ def test_joint_attention_stream_k_tail(ops, B, H, P, T, C, sms):
         assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1])
 
 
+@pytest.mark.parametrize("B,H,P,T,C,mode", [(1, 2, 1024, 256, 32, 0), (2, 3, 256, 256, 4, 0), (1, 2, 2200, 200, 5, 0),
+                                            (1, 1, 200, 100, 1, 0), (1, 2, 144, 72, 3, 1)])
+def test_joint_attention_optimistic_max_is_bit_identical(ops, B, H, P, T, C, mode):
+    """impl 13 starts each tile's exp2 with the row max already in use and checks the exchanged
+    max afterwards, redoing the tile when it grew past the lazy-rescale threshold: same maths
+    in every case, so the output must equal the plain kernel's bit for bit — also with scores
+    that keep growing along the keys (forces the redo path on many tiles)."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    N = P + T + C
+    q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((40, 1.5), (41, 1.0), (42, 1.0)))
+    ramp = torch.linspace(0.2, 6.0, N, device="cuda").view(1, 1, N, 1)          # later keys score higher
+    for kk in (k, (k.float() * ramp).to(BF16)):
+        outs = {}
+        for impl in (0, 13):
+            lib.ca_debug_set_attention_impl(impl)
+            try:
+                outs[impl] = ops.joint_attention(q, kk, v, P, T, C, mode)
+                torch.cuda.synchronize()
+            finally:
+                lib.ca_debug_set_attention_impl(0)
+        assert torch.equal(outs[0][0], outs[13][0]) and torch.equal(outs[0][1], outs[13][1])
+    ri, rt = _attention_oracle(q.float().cpu(), k.float().cpu(), v.float().cpu(), P, T, C, mode)
+    close(outs[13][0] if False else ops.joint_attention(q, k, v, P, T, C, mode)[0], ri, rtol=2e-2, atol=1e-2)
+
+
 def test_joint_attention_one_way(ops):
     """Image and text rows must not depend on the concept tokens at all (bit-exact)."""
     B, H, P, T, C = 1, 2, 384, 128, 5
