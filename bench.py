@@ -179,6 +179,8 @@ def run_ours(args, rank, world, local_rank):
     gen.model.use_graphs = not args.no_graphs
     if args.no_side_stream:
         gen.model.use_side_stream = False
+    if args.tp_overlap:
+        gen.model.overlap_allreduce = True
     for i in range(args.warmup):
         device_step(i)
     # graph capture empties the caching allocator's pools (torch.cuda.graph calls empty_cache):
@@ -377,6 +379,8 @@ def main():
     ap.add_argument("--config", default="schnell-1024", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel individually (A/B)")
+    ap.add_argument("--tp-overlap", action="store_true",
+                    help="head-sharded mode: two token chunks on two streams around the all-reduces (A/B)")
     ap.add_argument("--no-side-stream", action="store_true", help="text stream on the main CUDA stream (A/B)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

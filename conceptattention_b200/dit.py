@@ -216,6 +216,12 @@ class FluxDiTEngine:
         # communicator must see its collectives from one stream).
         self.use_side_stream = head_shard is None or head_shard.world == 1
         self.skip_unused_tail = True      # see the double-block loop (encode path only)
+        # head-sharded mode: two token chunks on two streams so one chunk computes while the other's
+        # partial sums are in the all-reduce.  Measured on 8 GPUs (config 5): 315 -> 353 ms per image
+        # (twice the launches; the ranks are launch-bound at 2 host cores each) -> off by default.
+        self.overlap_allreduce = False
+        self.tp_chunk_min_rows = 2048
+        self._tp_side = None
         self._side = None
         self.max_graphs = 8
         self._graphs, self._graph_seen, self._graph_pool = {}, {}, None
@@ -296,7 +302,7 @@ class FluxDiTEngine:
                     stop_after_multimodal_attentions=stop_after_multimodal_attentions,
                     joint_attention_kwargs=joint_attention_kwargs, accumulator=accumulator,
                     collect_vectors=collect_vectors)
-        eligible = (self.use_graphs and not collect_vectors and self.hs is None
+        eligible = (self.use_graphs and not collect_vectors and (self.hs is None or self.hs.graph_safe())
                     and ops.ATTN_EVENTS is None
                     and (accumulator is None or accumulator.per_pair is None)
                     and concept_vec is not None and img.ndim == 3 and txt.ndim == 3
@@ -400,6 +406,24 @@ class FluxDiTEngine:
             side = self._side
         main = torch.cuda.current_stream(dev)
 
+        # Head-sharded mode: every row-parallel GEMM is followed by an all-reduce that is several
+        # times longer than the GEMM itself.  The post-attention chains are row-wise, so they
+        # run as TWO token chunks on two CUDA streams: while one chunk's partial sums are in
+        # the NCCL all-reduce, the other chunk computes (GEMMs, K1c).  One GPU: one chunk.
+        def chunked(n_rows, fn):
+            """fn(r0, r1) over [0, n_rows); two chunks on (main, tp stream) when sharded."""
+            if not sharded or B != 1 or n_rows < self.tp_chunk_min_rows or not self.overlap_allreduce:
+                fn(0, n_rows)
+                return
+            if self._tp_side is None:
+                self._tp_side = torch.cuda.Stream(device=dev)
+            mid = (n_rows // 2 + 127) // 128 * 128
+            self._tp_side.wait_stream(main)
+            with torch.cuda.stream(self._tp_side):
+                fn(mid, n_rows)
+            fn(0, mid)
+            main.wait_stream(self._tp_side)
+
         def txt_chain(i, attn_tc):
             """proj -> gated residual + LN -> MLP -> gated residual (+ next block's LN) -> next
             block's qkv GEMM, all on the text+concept rows; returns the next tc_qkv (or None)."""
@@ -467,14 +491,24 @@ class FluxDiTEngine:
             else:
                 tc_qkv = txt_chain(i, attn_tc)
             o = off(pre + ".img_mod.lin")
-            proj = self._lin_rp(pre + ".img_attn.proj", attn_img)
-            h = ops.gate_residual_ln_modulate(x_img, proj, m_vec, None, None, o + 2 * D, o + 3 * D, o + 4 * D)
-            h = self._lin_rp(pre + ".img_mlp.2", self._lin_gelu(pre + ".img_mlp.0", h))
-            if i + 1 < p.depth:
-                on = off(f"double_blocks.{i + 1}.img_mod.lin")
-                ln["img"] = ops.gate_residual_ln_modulate(x_img, h, m_vec, None, None, o + 5 * D, on, on + D)
-            else:
-                ops.gate_residual_ln_modulate(x_img, h, m_vec, None, None, o + 5 * D, 0, 0, want_out=False)
+            last = i + 1 == p.depth
+            on = 0 if last else off(f"double_blocks.{i + 1}.img_mod.lin")
+            ln_next = None if last else torch.empty_like(x_img)
+
+            def img_rows(r0, r1, o=o, on=on, last=last, ln_next=ln_next, attn_img=attn_img, pre=pre):
+                xr = x_img[:, r0:r1]
+                proj = self._lin_rp(pre + ".img_attn.proj", attn_img[:, r0:r1])
+                h = ops.gate_residual_ln_modulate(xr, proj, m_vec, None, None, o + 2 * D, o + 3 * D, o + 4 * D)
+                h = self._lin_rp(pre + ".img_mlp.2", self._lin_gelu(pre + ".img_mlp.0", h))
+                if last:
+                    ops.gate_residual_ln_modulate(xr, h, m_vec, None, None, o + 5 * D, 0, 0, want_out=False)
+                else:
+                    ops.gate_residual_ln_modulate(xr, h, m_vec, None, None, o + 5 * D, on, on + D,
+                                                  out=ln_next[:, r0:r1])
+
+            chunked(P, img_rows)
+            if not last:
+                ln["img"] = ln_next
         if side is not None and p.depth:
             main.wait_stream(side)                       # txtc is final
         if collect_vectors:
@@ -502,14 +536,23 @@ class FluxDiTEngine:
                 ops.joint_attention(q, k, v, P, T, 0, _cabi.ATTN_BOTH, attn[:, :P], attn[:, P:])
             else:
                 attn = torch.cat(ops.joint_attention(q, k, v, P, T, 0), 1)
-            # linear2 over cat(attn, gelu(mlp)) as two accumulating GEMMs (row-parallel when sharded)
-            out = self._lin_rp(pre + ".linear2a", attn, bias_key=pre + ".linear2.bias",
-                               extra=(g, self.sd[pre + ".linear2b.weight"]))
-            if i + 1 < p.depth_single_blocks:
-                on = off(f"single_blocks.{i + 1}.modulation.lin")
-                xm = ops.gate_residual_ln_modulate(x, out, m_vec, None, None, o + 2 * D, on, on + D)
-            else:
-                ops.gate_residual_ln_modulate(x, out, m_vec, None, None, o + 2 * D, 0, 0, want_out=False)
+            last = i + 1 == p.depth_single_blocks
+            on = 0 if last else off(f"single_blocks.{i + 1}.modulation.lin")
+            xm_next = None if last else torch.empty_like(x)
+
+            def rows(r0, r1, o=o, on=on, last=last, xm_next=xm_next, attn=attn, g=g, pre=pre):
+                # linear2 over cat(attn, gelu(mlp)) as two accumulating GEMMs (row-parallel when sharded)
+                out = self._lin_rp(pre + ".linear2a", attn[:, r0:r1], bias_key=pre + ".linear2.bias",
+                                   extra=(g[:, r0:r1], self.sd[pre + ".linear2b.weight"]))
+                if last:
+                    ops.gate_residual_ln_modulate(x[:, r0:r1], out, m_vec, None, None, o + 2 * D, 0, 0,
+                                                  want_out=False)
+                else:
+                    ops.gate_residual_ln_modulate(x[:, r0:r1], out, m_vec, None, None, o + 2 * D, on, on + D,
+                                                  out=xm_next[:, r0:r1])
+
+            chunked(N, rows)
+            xm = xm_next
         x = x[:, :P].contiguous()
         o = off("final_layer.adaLN_modulation.1")                                 # shift | scale
         pred = self._lin("final_layer.linear", ops.ln_modulate(x, m_vec, None, None, o, o + D))

@@ -154,6 +154,11 @@ class HeadShard:
         use the list form and stage CUDA tensors through the host.  NCCL runs on device."""
         return dist.get_backend(self.group) == "gloo"
 
+    def graph_safe(self) -> bool:
+        """True when the collectives can be captured into a CUDA graph (NCCL on device; the gloo
+        path stages through the host)."""
+        return self.world == 1 or not self._gloo()
+
     def all_gather(self, x: torch.Tensor, dim: int) -> torch.Tensor:
         """Concatenate the ranks' `x` along `dim` in rank order.  Bit-exact: pure data movement."""
         if self.world == 1:

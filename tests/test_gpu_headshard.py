@@ -49,7 +49,28 @@ def _worker(rank, world, port, ret):
         sharded = run(FluxDiTEngine(p, sd, "cuda:0", head_shard=HeadShard(rank, world, p.num_heads)))
         tight = run(FluxDiTEngine(p, sd, "cuda:0",
                                   head_shard=HeadShard(rank, world, p.num_heads, reduce_fp32=True)))
+        # B = 1 with the two-chunk / two-stream overlap of the row-parallel all-reduces forced on
+        # (tiny P): same engine with and without chunking
+        inp1 = gi.dit_inputs(p, gi.TINY_SIDE, gi.TINY_T, gi.TINY_C, gi.INPUT_SEED, batch=1)
+        t1 = torch.full((1,), 0.75)
+
+        def run1(engine):
+            acc = HeatmapAccumulator(1, gi.TINY_C, P, "cuda:0", [0, 2], None)
+            pred, _ = engine(img=inp1["img"], img_ids=inp1["img_ids"], txt=inp1["txt"],
+                             txt_ids=inp1["txt_ids"], concepts=inp1["concepts"],
+                             concept_ids=inp1["concept_ids"], concept_vec=inp1["concept_vec"],
+                             y=inp1["vec"], timesteps=t1, accumulator=acc, collect_vectors=False)
+            out, cross = acc.finalize()
+            return pred.float().cpu(), out.cpu(), cross.cpu()
+
+        eng = FluxDiTEngine(p, sd, "cuda:0", head_shard=HeadShard(rank, world, p.num_heads))
+        eng.overlap_allreduce = False
+        plain1 = run1(eng)
+        eng.overlap_allreduce, eng.tp_chunk_min_rows = True, 128
+        chunk1 = run1(eng)
+        assert eng._tp_side is not None                     # the chunked path really ran
         if rank == 0:
+            ret["plain1"], ret["chunk1"] = plain1, chunk1
             ret["sharded"], ret["tight"] = sharded, tight
             ret["full"] = run(FluxDiTEngine(p, sd, "cuda:0"))
             # fp32 oracle of the same forward: the yardstick for the bf16 noise floor
@@ -95,3 +116,10 @@ def test_head_sharded_engine_matches_unsharded():
             assert mae(got, ora) <= 1.5 * mae(ref, ora) + 1e-4, (name, tag, mae(got, ora), mae(ref, ora))
             assert relf(got, ora) <= max(1e-2, 2.0 * relf(ref, ora)), (name, tag, relf(got, ora), relf(ref, ora))
         assert ((pred_x - pred_f).abs().max() / pred_f.abs().max()).item() < 5e-2, name
+    # token-chunked overlap: same maths on row subsets (cuBLAS may pick another kernel per M)
+    for a, b_, tag in zip(ret["chunk1"], ret["plain1"], ("pred", "output", "cross")):
+        if tag == "pred":
+            assert ((a - b_).abs().max() / b_.abs().max()).item() < 2e-2
+        else:
+            assert (a.argmax(1) == b_.argmax(1)).float().mean().item() >= 0.999
+            assert mae(a, b_) < 1e-3, (tag, mae(a, b_))
