@@ -38,6 +38,7 @@ SIGNATURES = {
     "ca_gaussian_blur3": [_p, _p, _i, _i, _i, _p],
     "ca_argmax_mask": [_p, _p, _i, _i, _i, _i, _p],
     "ca_binary_masks": [_p, _p, _i, _i, _p],
+    "ca_segmentation_counts": [_p, _p, _i64, _i, _p, _p],
     "ca_heatmaps_from_vectors_host": [_p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _i, _i, _p],
 }
 _RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p,

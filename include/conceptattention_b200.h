@@ -168,6 +168,16 @@ ca_status ca_argmax_mask(const float* heat, int64_t* mask, int B, int C, int P,
 /* mask[m,p] = heat[m,p] > mean_p(heat[m,:])   (segmentation.py:60-61). M = B*C maps. */
 ca_status ca_binary_masks(const float* heat, uint8_t* mask, int M, int P, void* stream);
 
+/* ---- K6: segmentation-metric counters ------------------------
+ * One pass over a predicted and a ground-truth label map (integer-valued floats, ignore label -1)
+ * replaces the reference's host-side numpy counting (concept_attention/utils.py:71-85
+ * batch_pix_accuracy and :88-108 batch_intersection_union, which shift labels by +1 and histogram
+ * over (1, nclass)).  counts is device memory, uint64 [2 + 3*nclass], overwritten:
+ *   [0] pixel_correct  [1] pixel_labeled  [2..) area_inter[nclass], area_pred[nclass], area_lab[nclass]
+ * (area_union = area_pred + area_lab - area_inter is left to the caller, as in the reference). */
+ca_status ca_segmentation_counts(const float* predict, const float* target, int64_t n, int nclass,
+                                 uint64_t* counts, void* stream);
+
 /* ---- host-buffer form of compute_heatmaps_from_vectors (:29-91) --------------
  * image_host  bf16 [Nt,L,B,P,K]   (or per-head [Nt,L,B,H,P,d] when per_head != 0)
  * concept_host bf16 [Nt,L,B,C,K]  (or [Nt,L,B,H,C,d])

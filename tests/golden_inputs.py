@@ -58,3 +58,25 @@ def mask_inputs():
     """[5,16,16] coefficients quantised to 1/4 so the argmax has many exact ties."""
     g = torch.Generator().manual_seed(99)
     return torch.round(torch.randn(5, 16, 16, generator=g) * 2) / 4
+
+
+def metric_inputs():
+    """Seeded label maps / scores for the segmentation metrics (utils.py:48-108).
+
+    binary: the (1 - mask, mask) float stacks of experiments/imagenet_segmentation/run_experiment.py:206-214
+    voc:    integer labels 0..20 with the ignore label -1 (nclass = 21)
+    ap:     scores quantised to 1/16 (many ties) + labels with some ignored pixels
+    """
+    g = torch.Generator().manual_seed(1234)
+    m = (torch.rand(224, 224, generator=g) > 0.6).float()
+    t = (torch.rand(224, 224, generator=g) > 0.5).float()
+    binary = (torch.stack((1 - m, m)), torch.stack((1 - t, t)), 2)
+    vp = torch.randint(0, 21, (3, 64, 64), generator=g).float()
+    vt = torch.randint(-1, 21, (3, 64, 64), generator=g).float()
+    vp = torch.where(torch.rand(3, 64, 64, generator=g) > 0.5, vt.clamp(min=0), vp)   # ~half correct
+    voc = (vp, vt, 21)
+    c = torch.round(torch.rand(2, 64, 64, generator=g) * 16) / 16
+    lab = (torch.rand(2, 64, 64, generator=g) > 0.7).float()
+    lab[0, :4] = -1.0                                                                # ignored rows
+    ap = (torch.stack((1 - c, c), dim=1), lab)                                       # [2,2,64,64], [2,64,64]
+    return {"binary": binary, "voc": voc, "ap": ap}

@@ -113,3 +113,31 @@ def test_unpinned_normalisers_properties():
     r = (z / 2 - torch.sqrt(p))
     tau = (r * (p > 0)).sum(-1) / (p > 0).sum(-1)
     assert ((r - tau[:, None]).abs() * (p > 0)).max() < 1e-5
+
+
+def test_segmentation_metrics_match_reference(golden_dir):
+    """oracle/metrics.py against the reference's utils.py:48-108 outputs (make_golden_metrics.py)."""
+    from oracle import metrics as om
+    g = np.load(os.path.join(golden_dir, "metrics.npz"))
+    cases = gi.metric_inputs()
+    for name in ("binary", "voc"):
+        pred, tgt, nclass = cases[name]
+        assert om.pix_accuracy(pred.numpy(), tgt.numpy()) == (int(g[name + "_correct"]), int(g[name + "_labeled"]))
+        inter, union = om.intersection_union(pred.numpy(), tgt.numpy(), nclass)
+        assert np.array_equal(inter, g[name + "_inter"]) and np.array_equal(union, g[name + "_union"])
+    scores, labels = cases["ap"]
+    np.testing.assert_allclose(om.ap_scores(scores.numpy(), labels.numpy()), g["ap"], rtol=0, atol=1e-12)
+
+
+def test_average_precision_matches_sklearn_on_edge_cases():
+    """The AP restatement against scikit-learn itself (the reference's dependency, utils.py:66)."""
+    skm = pytest.importorskip("sklearn.metrics")
+    from oracle import metrics as om
+    rng = np.random.default_rng(3)
+    for n, levels in ((1, 2), (17, 2), (500, 4), (4096, 1000), (4096, 10 ** 9)):
+        s = np.round(rng.random(n) * levels) / levels
+        y = (rng.random(n) > 0.6).astype(np.float64)
+        y[0] = 1.0
+        assert abs(om.average_precision(y, s) - skm.average_precision_score(y, s)) < 1e-12, (n, levels)
+    s = rng.random(64)
+    assert abs(om.average_precision(np.ones(64), s) - 1.0) < 1e-12      # all positive
