@@ -134,7 +134,8 @@ def run_ours(args, rank, world, local_rank):
     hs = None
     if sharded:
         from conceptattention_b200.weights import CONFIGS
-        hs = HeadShard(rank, world, CONFIGS[wl["model"]].num_heads)
+        hs = HeadShard(rank, world, CONFIGS[wl["model"]].num_heads,
+                       sequence_parallel=args.hs_mode == "sequence")
     pipe = ConceptAttentionFluxPipeline(model_name=wl["model"], device=dev, seed=0 if sharded else rank,
                                         head_shard=hs)
     gen = pipe.flux_generator
@@ -282,9 +283,12 @@ def run_ours(args, rank, world, local_rank):
                                f"{mode}: {nsteps if mode == 'generate' else 1} DiT pass(es) x ({blocks}), heatmaps from "
                                f"layers {layers[0]}..{layers[-1]} both spaces",
                    "images_per_step_per_gpu": batch,
-                   "parallelism": (f"heads sharded {H}/{world} per GPU with the linears tensor-parallel around them; "
-                                   f"NCCL all-reduce of partial heatmap logits and of the row-parallel "
-                                   f"proj/MLP partial sums") if sharded else
+                   "parallelism": ((f"heads sharded {H}/{world} per GPU inside the attention, every token-wise op "
+                                    f"on 1/{world} of the rows with replicated weights; two NCCL all-to-alls "
+                                    f"per block") if args.hs_mode == "sequence" else
+                                   (f"heads sharded {H}/{world} per GPU with the linears tensor-parallel around them; "
+                                    f"NCCL all-reduce of partial heatmap logits and of the row-parallel "
+                                    f"proj/MLP partial sums")) if sharded else
                                   f"dp{world} (one image stream per GPU, no collective on the data path)",
                    "cache": "inputs larger than L2: 23.8 GB of bf16 weights stream through every step"},
         "e2e": {"value": images / (ms_e2e * 1e-3), "unit": "images/s",
@@ -379,6 +383,9 @@ def main():
     ap.add_argument("--config", default="schnell-1024", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel individually (A/B)")
+    ap.add_argument("--hs-mode", choices=("tensor", "sequence"), default="tensor",
+                    help="head-sharded workloads: tensor-parallel linears, or sequence-parallel rows "
+                         "with the head split only inside the attention")
     ap.add_argument("--tp-overlap", action="store_true",
                     help="head-sharded mode: two token chunks on two streams around the all-reduces (A/B)")
     ap.add_argument("--no-side-stream", action="store_true", help="text stream on the main CUDA stream (A/B)")

@@ -39,6 +39,10 @@ SIGNATURES = {
     "ca_argmax_mask": [_p, _p, _i, _i, _i, _i, _p],
     "ca_binary_masks": [_p, _p, _i, _i, _p],
     "ca_segmentation_counts": [_p, _p, _i64, _i, _p, _p],
+    "ca_qkv_prep_grouped": [_p, _i64, _i, _p, _i64, _i, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p, _i, _i64, _p],
+    "ca_seq_unpack_qkv": [_p, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p],
+    "ca_seq_pack_out": [_p, _p, _i, _i, _i, _i, _i, _p, _p],
+    "ca_seq_unpack_out": [_p, _i, _i, _i, _i, _i, _p, _p, _p],
     "ca_heatmaps_from_vectors_host": [_p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _i, _i, _p],
 }
 _RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p,

@@ -18,7 +18,7 @@ CSRC = os.path.join(PKG, "csrc")
 OBJ = os.path.join(PKG, "build")
 LIB = os.path.join(PKG, "libconceptattention_b200.so")
 SOURCES = ["ca_api.cu", "k1_prep.cu", "k2_attention.cu", "k3_heatmap.cu", "k3_heatmap_tc.cu", "k5_masks.cu",
-           "k6_metrics.cu"]
+           "k6_metrics.cu", "k7_seqpar.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--use_fast_math", "-Xptxas", "-v"]

@@ -350,7 +350,8 @@ qkv_prep_kernel(const __nv_bfloat16* __restrict__ qkv_a, int64_t stride_a, int N
                 const __nv_bfloat16* __restrict__ qs_b, const __nv_bfloat16* __restrict__ ks_b,
                 const float* __restrict__ rope, int B, int H,
                 __nv_bfloat16* __restrict__ q, __nv_bfloat16* __restrict__ k,
-                __nv_bfloat16* __restrict__ v, __nv_bfloat16* __restrict__ q_pre) {
+                __nv_bfloat16* __restrict__ v, __nv_bfloat16* __restrict__ q_pre,
+                int group_heads, int64_t group_stride) {
   const int hp_per_tok = (H + 1) >> 1;
   const int64_t warp = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int Ntot = Na + Nb;
@@ -398,6 +399,11 @@ qkv_prep_kernel(const __nv_bfloat16* __restrict__ qkv_a, int64_t stride_a, int N
   if (!active) return;
   const int64_t dst = (((int64_t)b * H + h) * Ntot + n) * CA_HEAD_DIM + ch * 8;
   if (q_pre) *reinterpret_cast<uint4*>(q_pre + dst) = pack8(fq);
+  // grouped form (sequence-parallel exchange): heads [g*G, (g+1)*G) of q, k and v go to group g's
+  // slab, so each destination rank's chunk of the all-to-all send buffer is contiguous
+  const int64_t dst_g = group_heads
+      ? (int64_t)(h / group_heads) * group_stride + ((int64_t)(h % group_heads) * Ntot + n) * CA_HEAD_DIM + ch * 8
+      : dst;
   // RoPE: pairs (2i,2i+1); out0 = cos*x0 - sin*x1, out1 = sin*x0 + cos*x1   (math.py:19-30)
   const float4* rp = reinterpret_cast<const float4*>(rope + ((int64_t)n * 64 + ch * 4) * 2);
   const float4 r0 = rp[0], r1 = rp[1];
@@ -410,9 +416,9 @@ qkv_prep_kernel(const __nv_bfloat16* __restrict__ qkv_a, int64_t stride_a, int N
     ok[2 * i] = cs[i] * fk[2 * i] - sn[i] * fk[2 * i + 1];
     ok[2 * i + 1] = sn[i] * fk[2 * i] + cs[i] * fk[2 * i + 1];
   }
-  *reinterpret_cast<uint4*>(q + dst) = pack8(oq);
-  *reinterpret_cast<uint4*>(k + dst) = pack8(ok);
-  *reinterpret_cast<uint4*>(v + dst) = uv;
+  *reinterpret_cast<uint4*>(q + dst_g) = pack8(oq);
+  *reinterpret_cast<uint4*>(k + dst_g) = pack8(ok);
+  *reinterpret_cast<uint4*>(v + dst_g) = uv;
 }
 
 }  // namespace ca
@@ -437,12 +443,17 @@ extern "C" ca_status ca_gate_residual_ln_modulate(void* x, const void* y, int64_
                              shift_off, scale_off, (cudaStream_t)stream);
 }
 
-extern "C" ca_status ca_qkv_prep(const void* qkv_a, int64_t row_stride_a, int Na, const void* qkv_b,
-                                 int64_t row_stride_b, int Nb, const void* q_scale_a,
-                                 const void* k_scale_a, const void* q_scale_b,
-                                 const void* k_scale_b, const float* rope, int B, int H, void* q,
-                                 void* k, void* v, void* q_pre, void* stream) {
+extern "C" ca_status ca_qkv_prep_grouped(const void* qkv_a, int64_t row_stride_a, int Na,
+                                         const void* qkv_b, int64_t row_stride_b, int Nb,
+                                         const void* q_scale_a, const void* k_scale_a,
+                                         const void* q_scale_b, const void* k_scale_b,
+                                         const float* rope, int B, int H, void* q, void* k, void* v,
+                                         void* q_pre, int group_heads, int64_t group_stride,
+                                         void* stream) {
   using namespace ca;
+  if (group_heads < 0 || (group_heads > 0 && (B != 1 || H % group_heads || group_stride % 8 ||
+                                              group_stride < (int64_t)group_heads * (Na + Nb) * CA_HEAD_DIM)))
+    return CA_ERR_INVALID_ARG;
   if (Na < 0 || Nb < 0 || B < 0 || H <= 0 || !q || !k || !v || !rope) return CA_ERR_INVALID_ARG;
   if ((Na > 0 && (!qkv_a || !q_scale_a || !k_scale_a)) ||
       (Nb > 0 && (!qkv_b || !q_scale_b || !k_scale_b)))
@@ -462,7 +473,17 @@ extern "C" ca_status ca_qkv_prep(const void* qkv_a, int64_t row_stride_a, int Na
       (const __nv_bfloat16*)qkv_a, row_stride_a, Na, (const __nv_bfloat16*)qkv_b, row_stride_b, Nb,
       (const __nv_bfloat16*)q_scale_a, (const __nv_bfloat16*)k_scale_a,
       (const __nv_bfloat16*)q_scale_b, (const __nv_bfloat16*)k_scale_b, rope, B, H,
-      (__nv_bfloat16*)q, (__nv_bfloat16*)k, (__nv_bfloat16*)v, (__nv_bfloat16*)q_pre);
+      (__nv_bfloat16*)q, (__nv_bfloat16*)k, (__nv_bfloat16*)v, (__nv_bfloat16*)q_pre, group_heads,
+      group_stride);
   CA_LAUNCH_CHECK();
   return CA_OK;
+}
+
+extern "C" ca_status ca_qkv_prep(const void* qkv_a, int64_t row_stride_a, int Na, const void* qkv_b,
+                                 int64_t row_stride_b, int Nb, const void* q_scale_a,
+                                 const void* k_scale_a, const void* q_scale_b,
+                                 const void* k_scale_b, const float* rope, int B, int H, void* q,
+                                 void* k, void* v, void* q_pre, void* stream) {
+  return ca_qkv_prep_grouped(qkv_a, row_stride_a, Na, qkv_b, row_stride_b, Nb, q_scale_a, k_scale_a,
+                             q_scale_b, k_scale_b, rope, B, H, q, k, v, q_pre, 0, 0, stream);
 }

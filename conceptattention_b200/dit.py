@@ -204,8 +204,8 @@ class FluxDiTEngine:
             o, m = self.mod_off[n]
             self.mod_w[o:o + m].copy_(self.sd.pop(n + ".weight"))
             self.mod_b[o:o + m].copy_(self.sd.pop(n + ".bias"))
-        if self.hs is not None and self.hs.world > 1:
-            self.hs.shard_state_dict(self.sd, params)
+        if self.hs is not None and self.hs.world > 1 and not self.hs.sequence_parallel:
+            self.hs.shard_state_dict(self.sd, params)       # sequence-parallel: weights stay whole
         self._rope_cache = {}
         # CUDA graphs of whole forwards (one per signature), captured the second time a
         # signature is seen; the first call runs launch by launch and warms cuBLAS.
@@ -233,7 +233,7 @@ class FluxDiTEngine:
         columns and b is zero on ranks > 0.  `hs.reduce_fp32` keeps the partial sums in fp32
         through the all-reduce (one bf16 rounding, as on one GPU) at twice the NVLink bytes."""
         w, b = self.sd[prefix + ".weight"], self.sd.get(bias_key or prefix + ".bias")
-        sharded = self.hs is not None and self.hs.world > 1
+        sharded = self.hs is not None and self.hs.world > 1 and not self.hs.sequence_parallel
         x2 = x.reshape(-1, x.shape[-1])
         if sharded and self.hs.reduce_fp32:
             y = torch.mm(x2, w.t(), out_dtype=torch.float32)
@@ -378,10 +378,25 @@ class FluxDiTEngine:
                 v = v + self._mlp_embed("guidance_in", timestep_embedding(to(guidance), 256))
             return v + self._mlp_embed("vector_in", pooled)
 
+        rope = self._rope(img_ids, txt_ids, concept_ids)
+        sharded = self.hs is not None and self.hs.world > 1
+        seqpar = sharded and self.hs.sequence_parallel
+        if seqpar:
+            # sequence-parallel: from here on P and T are THIS RANK's row counts; only the
+            # attention (see `attend`) sees all rows, for this rank's heads
+            W, rk = self.hs.world, self.hs.rank
+            if B != 1 or P % W or T % W:
+                raise ValueError(f"sequence-parallel mode needs B = 1 and P, T divisible by {W} (got {B}, {P}, {T})")
+            Pg, Tg, P, T = P, T, P // W, T // W
+            img, txt = img[:, rk * P:(rk + 1) * P], txt[:, rk * T:(rk + 1) * T]
+            if self._rope_cache.get("local_key") != (rope.data_ptr(), W, rk, P, T):
+                self._rope_cache["local"] = torch.cat(
+                    (rope[rk * P:(rk + 1) * P], rope[Pg + rk * T:Pg + (rk + 1) * T], rope[Pg + Tg:]), 0).contiguous()
+                self._rope_cache["local_key"] = (rope.data_ptr(), W, rk, P, T)
+            rope = self._rope_cache["local"]                 # rows [img_l | txt_l | concept]
         x_img = self._lin("img_in", img).contiguous()
         vec, cvec = cond(y), cond(concept_vec)
         txtc = self._lin("txt_in", torch.cat((txt, concepts), 1)).contiguous()   # [B,T+C,D]
-        rope = self._rope(img_ids, txt_ids, concept_ids)
         svec = F.silu(torch.cat((vec, cvec), 0))                                  # [2B,D]
         mods = F.linear(svec, self.mod_w, self.mod_b)                             # [2B,Mtot]
 
@@ -391,8 +406,8 @@ class FluxDiTEngine:
         off = lambda name: self.mod_off[name][0]
 
         collected = {k: [] for k in VECTOR_KEYS} if collect_vectors else None
-        sharded = self.hs is not None and self.hs.world > 1
-        Hl = self.hs.h_local if sharded else H                   # heads computed on this rank
+        tp = sharded and not seqpar                              # tensor-parallel linears
+        Hl = self.hs.h_local if tp else H                        # heads of the qkv GEMMs on this rank
         # LN + modulate of block 0; later blocks get theirs fused into the previous block's last
         # gated-residual kernel (K1c with the NEXT block's shift/scale): one pass over x less per
         # block boundary
@@ -412,7 +427,7 @@ class FluxDiTEngine:
         # the NCCL all-reduce, the other chunk computes (GEMMs, K1c).  One GPU: one chunk.
         def chunked(n_rows, fn):
             """fn(r0, r1) over [0, n_rows); two chunks on (main, tp stream) when sharded."""
-            if not sharded or B != 1 or n_rows < self.tp_chunk_min_rows or not self.overlap_allreduce:
+            if not tp or B != 1 or n_rows < self.tp_chunk_min_rows or not self.overlap_allreduce:
                 fn(0, n_rows)
                 return
             if self._tp_side is None:
@@ -423,6 +438,23 @@ class FluxDiTEngine:
                 fn(mid, n_rows)
             fn(0, mid)
             main.wait_stream(self._tp_side)
+
+        def attend(qkv_a, qkv_b, scales_a, scales_b, rope_x, n_con, amode, want_q_pre=False, out=None):
+            """K1b + K2 -> (attn_img [B,P,*], attn_tc [B,T+n_con,*], q_pre | None) for this rank's
+            rows.  Sequence-parallel: K1b writes the all-to-all send buffer, K2 runs this rank's
+            heads over ALL rows, a second all-to-all brings back every head of the local rows."""
+            if not seqpar:
+                res = ops.qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope_x, Hl, want_q_pre=want_q_pre)
+                o = (None, None) if out is None else out
+                a_img, a_tc = ops.joint_attention(res[0], res[1], res[2], P, T, n_con, amode, o[0], o[1])
+                return a_img, a_tc, (res[3] if want_q_pre else None)
+            send, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H,
+                                               self.hs.h_local, want_q_pre=want_q_pre)
+            q, k, v = ops.seq_unpack_qkv(self.hs.all_to_all(send), rk, P, T, n_con)
+            o_img, o_tc = ops.joint_attention(q, k, v, Pg, Tg, n_con, amode)
+            back = self.hs.all_to_all(ops.seq_pack_out(o_img, o_tc, W, P, T, n_con))
+            a_img, a_tc = ops.seq_unpack_out(back, P, T, n_con, out)
+            return a_img, a_tc, q_pre
 
         def txt_chain(i, attn_tc):
             """proj -> gated residual + LN -> MLP -> gated residual (+ next block's LN) -> next
@@ -446,16 +478,19 @@ class FluxDiTEngine:
             img_qkv = self._lin(pre + ".img_attn.qkv", ln["img"])
             if side is not None and i > 0:
                 main.wait_stream(side)                   # join: tc_qkv (and txtc) of the side branch
-            res = ops.qkv_prep(
+            attn_img, attn_tc, q_pre = attend(
                 img_qkv, tc_qkv,
                 (self.sd[pre + ".img_attn.norm.query_norm.scale"], self.sd[pre + ".img_attn.norm.key_norm.scale"]),
                 (self.sd[pre + ".txt_attn.norm.query_norm.scale"], self.sd[pre + ".txt_attn.norm.key_norm.scale"]),
-                rope, Hl, want_q_pre=sel)
-            q, k, v = res[:3]
-            attn_img, attn_tc = ops.joint_attention(q, k, v, P, T, C, mode)     # this rank's heads
-            q_pre = res[3] if sel else None
+                rope, C, mode, want_q_pre=sel)
             if sel and accumulator is not None and accumulator.multiplicity(i) > 0:
-                if sharded:
+                if seqpar:
+                    # complete logits (all heads) of this rank's pixels, gathered along P (small)
+                    part = torch.empty(2, B, C, P, device=dev, dtype=torch.float32)
+                    ops.heatmap_logits(attn_img, attn_tc[:, T:], out=part[0])
+                    ops.heatmap_logits(q_pre[:, :, :P], q_pre[:, :, P + T:], per_head=True, out=part[1])
+                    accumulator.add_logits(i, self.hs.all_gather(part, -1))
+                elif tp:
                     # partial logits over this rank's heads, ONE all-reduce for both spaces
                     part = torch.empty(2, B, C, P, device=dev, dtype=torch.float32)
                     ops.heatmap_logits(attn_img, attn_tc[:, T:], out=part[0])
@@ -463,10 +498,15 @@ class FluxDiTEngine:
                     accumulator.add_logits(i, self.hs.all_reduce_sum(part))
                 else:
                     accumulator.add(i, attn_img, attn_tc[:, T:], q_pre, P, T)
-            if sharded and collect_vectors:
+            if tp and collect_vectors:
                 q_pre = self.hs.all_gather(q_pre, 1)
-            if sel and collect_vectors:
-                gather = (lambda t: self.hs.all_gather_heads(t)) if sharded else (lambda t: t)
+            if sel and collect_vectors and seqpar:         # image rows gathered along the token axis
+                collected["output_space_concept_vectors"].append(attn_tc[:, T:].clone())
+                collected["output_space_image_vectors"].append(self.hs.all_gather(attn_img, 1))
+                collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
+                collected["cross_attention_image_vectors"].append(self.hs.all_gather(q_pre[:, :, :P], 2))
+            elif sel and collect_vectors:
+                gather = (lambda t: self.hs.all_gather_heads(t)) if tp else (lambda t: t)
                 collected["output_space_concept_vectors"].append(gather(attn_tc[:, T:].clone()))
                 collected["output_space_image_vectors"].append(gather(attn_img))
                 collected["cross_attention_concept_vectors"].append(q_pre[:, :, P + T:].clone())
@@ -529,13 +569,12 @@ class FluxDiTEngine:
             o = off(pre + ".modulation.lin")
             h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3*Hl*128]
             g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M/G] gelu in epilogue
-            q, k, v = ops.qkv_prep(h, None, (self.sd[pre + ".norm.query_norm.scale"],
-                                             self.sd[pre + ".norm.key_norm.scale"]), None, rope_s, Hl)
+            scales = (self.sd[pre + ".norm.query_norm.scale"], self.sd[pre + ".norm.key_norm.scale"])
             if B == 1:
                 attn = torch.empty(1, N, Hl * 128, device=dev, dtype=BF16)
-                ops.joint_attention(q, k, v, P, T, 0, _cabi.ATTN_BOTH, attn[:, :P], attn[:, P:])
+                attend(h, None, scales, None, rope_s, 0, _cabi.ATTN_BOTH, out=(attn[:, :P], attn[:, P:]))
             else:
-                attn = torch.cat(ops.joint_attention(q, k, v, P, T, 0), 1)
+                attn = torch.cat(attend(h, None, scales, None, rope_s, 0, _cabi.ATTN_BOTH)[:2], 1)
             last = i + 1 == p.depth_single_blocks
             on = 0 if last else off(f"single_blocks.{i + 1}.modulation.lin")
             xm_next = None if last else torch.empty_like(x)
@@ -556,6 +595,8 @@ class FluxDiTEngine:
         x = x[:, :P].contiguous()
         o = off("final_layer.adaLN_modulation.1")                                 # shift | scale
         pred = self._lin("final_layer.linear", ops.ln_modulate(x, m_vec, None, None, o, o + D))
+        if seqpar:
+            pred = self.hs.all_gather(pred, 1)               # [1,P_local,*] -> all rows, rank order
         return pred, collected
 
     __call__ = forward

@@ -116,6 +116,82 @@ def qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope, H, want_q_pre=False):
     return (q, k, v, q_pre) if want_q_pre else (q, k, v)
 
 
+def qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope, H, G, want_q_pre=False):
+    """K1b for the sequence-parallel exchange (B = 1): same maths as `qkv_prep`, q/k/v written as
+    one send buffer [H/G, 3, G, N, 128] (chunk w = the q, k, v of rank w's G heads over this rank's
+    N rows).  Returns (send, q_pre | None); q_pre keeps [1, H, N, 128]."""
+    B, Na = qkv_a.shape[0], qkv_a.shape[1]
+    Nb = 0 if qkv_b is None else qkv_b.shape[1]
+    assert B == 1 and H % G == 0
+    for t in (qkv_a, qkv_b):
+        if t is not None:
+            assert t.is_cuda and t.dtype == BF16 and t.stride(-1) == 1
+    _req(rope, torch.float32, "rope")
+    assert rope.shape == (Na + Nb, 64, 2), rope.shape
+    N = Na + Nb
+    send = torch.empty(H // G, 3, G, N, 128, device=qkv_a.device, dtype=BF16)
+    q_pre = torch.empty(1, H, N, 128, device=qkv_a.device, dtype=BF16) if want_q_pre else None
+    sb = scales_b if scales_b is not None else (None, None)
+    slab = G * N * 128 * 2                                     # bytes of one [G,N,128] slab
+    check(_cabi.load().ca_qkv_prep_grouped(
+        qkv_a.data_ptr(), qkv_a.stride(1), Na,
+        qkv_b.data_ptr() if qkv_b is not None else None,
+        qkv_b.stride(1) if qkv_b is not None else 0, Nb,
+        scales_a[0].data_ptr(), scales_a[1].data_ptr(),
+        sb[0].data_ptr() if sb[0] is not None else None,
+        sb[1].data_ptr() if sb[1] is not None else None,
+        rope.data_ptr(), 1, H, send.data_ptr(), send.data_ptr() + slab, send.data_ptr() + 2 * slab,
+        q_pre.data_ptr() if want_q_pre else None, G, 3 * G * N * 128, _stream(qkv_a)),
+        "ca_qkv_prep_grouped")
+    return send, q_pre
+
+
+def seq_unpack_qkv(recv, self_rank, Pl, Tl, C):
+    """recv [W,3,Hl,Pl+Tl+C,128] (chunk w from rank w) -> q,k,v [1,Hl,W*(Pl+Tl)+C,128] in K2 row
+    order [img | txt | concept]; concept rows come from this rank's own chunk."""
+    _req(recv, BF16, "recv")
+    W, three, Hl, Nl, d = recv.shape
+    assert three == 3 and d == 128 and Nl == Pl + Tl + C
+    N = W * (Pl + Tl) + C
+    q, k, v = (torch.empty(1, Hl, N, 128, device=recv.device, dtype=BF16) for _ in range(3))
+    check(_cabi.load().ca_seq_unpack_qkv(recv.data_ptr(), W, self_rank, Hl, Pl, Tl, C, q.data_ptr(),
+                                         k.data_ptr(), v.data_ptr(), _stream(recv)), "ca_seq_unpack_qkv")
+    return q, k, v
+
+
+def seq_pack_out(out_img, out_txtc, W, Pl, Tl, C):
+    """K2 outputs [1,W*Pl,Hl*128], [1,W*Tl+C,Hl*128] -> send [W,Pl+Tl+C,Hl*128] (every chunk also
+    carries the C concept rows of this rank's heads)."""
+    _req(out_img, BF16, "out_img")
+    _req(out_txtc, BF16, "out_txtc")
+    Hl = out_img.shape[-1] // 128
+    assert out_img.shape[1] == W * Pl and out_txtc.shape[1] == W * Tl + C
+    send = torch.empty(W, Pl + Tl + C, Hl * 128, device=out_img.device, dtype=BF16)
+    check(_cabi.load().ca_seq_pack_out(out_img.data_ptr(), out_txtc.data_ptr(), W, Hl, Pl, Tl, C,
+                                       send.data_ptr(), _stream(out_img)), "ca_seq_pack_out")
+    return send
+
+
+def seq_unpack_out(recv, Pl, Tl, C, out=None):
+    """recv [W,Pl+Tl+C,Hl*128] (chunk w = heads of rank w) -> attn_img [1,Pl,W*Hl*128],
+    attn_tc [1,Tl+C,W*Hl*128]: this rank's rows with all heads."""
+    _req(recv, BF16, "recv")
+    W, Nl, K = recv.shape
+    assert Nl == Pl + Tl + C and K % 128 == 0
+    if out is not None:                      # caller-owned, dense rows of W*K elements
+        attn_img, attn_tc = out
+        for t, n in ((attn_img, Pl), (attn_tc, Tl + C)):
+            assert t.dtype == BF16 and t.shape[-2:] == (n, W * K) and t.stride(-1) == 1 and t.stride(-2) == W * K
+    else:
+        attn_img = torch.empty(1, Pl, W * K, device=recv.device, dtype=BF16)
+        attn_tc = torch.empty(1, Tl + C, W * K, device=recv.device, dtype=BF16)
+    check(_cabi.load().ca_seq_unpack_out(recv.data_ptr(), W, K // 128, Pl, Tl, C,
+                                         attn_img.data_ptr() if Pl else None,
+                                         attn_tc.data_ptr() if Tl + C else None, _stream(recv)),
+          "ca_seq_unpack_out")
+    return attn_img, attn_tc
+
+
 def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_txtc=None):
     """One-way joint attention over [img|txt|concept]; returns (out_img [B,P,H*128],
     out_txtc [B,T+C,H*128])."""

@@ -15,6 +15,10 @@ Two modes:
   (column-parallel qkv / mlp.0, row-parallel proj / mlp.2 / linear2) and carries the
   collective the path needs: all-reduce(SUM) of partial heatmap logits and of the
   row-parallel partial outputs (all-gather only when the caller wants the raw vectors).
+  `HeadShard(sequence_parallel=True)` is the second form of this mode: weights replicated,
+  every token-wise op on 1/world of the rows, heads split only inside the attention through two
+  all-to-alls per block (4x fewer NVLink bytes than the tensor-parallel all-reduces and no
+  replicated elementwise work).
 """
 from __future__ import annotations
 
@@ -87,6 +91,10 @@ class HeadShard:
     num_heads: int
     group: object = None
     reduce_fp32: bool = False     # row-parallel partial sums all-reduced in fp32 (tight parity mode)
+    # sequence-parallel form of the head-sharded mode: token-wise ops on 1/world of the rows with
+    # REPLICATED weights, heads split only inside the attention (two all-to-alls per block instead
+    # of an all-reduce after every row-parallel linear).  B = 1, rows divisible by world.
+    sequence_parallel: bool = False
 
     def __post_init__(self):
         if self.num_heads % self.world:
@@ -177,6 +185,21 @@ class HeadShard:
         shape = list(x.shape)
         shape[dim] *= self.world
         return out.permute(*perm).reshape(shape)
+
+    def all_to_all(self, x: torch.Tensor) -> torch.Tensor:
+        """x [world, ...] contiguous: chunk w goes to rank w; returns [world, ...] with chunk w
+        received from rank w.  Bit-exact: pure data movement."""
+        if self.world == 1:
+            return x
+        assert x.is_contiguous() and x.shape[0] == self.world
+        if self._gloo():
+            h = x.cpu().view(torch.uint8)                  # bytes: gloo has no bf16 all-to-all
+            out = torch.empty_like(h)
+            dist.all_to_all_single(out, h, group=self.group)
+            return out.view(x.dtype).view(x.shape).to(x.device)
+        out = torch.empty_like(x)
+        dist.all_to_all_single(out, x, group=self.group)
+        return out
 
     def all_gather_heads(self, x: torch.Tensor) -> torch.Tensor:
         """x [..., H_local*d] (this rank's heads) -> [..., H*d] with heads in rank order."""

@@ -93,6 +93,18 @@ ca_status ca_qkv_prep(const void* qkv_a, int64_t row_stride_a, int Na,
                       const void* q_scale_b, const void* k_scale_b,
                       const float* rope, int B, int H,
                       void* q, void* k, void* v, void* q_pre, void* stream);
+/* Grouped form for the sequence-parallel exchange (B = 1): heads [g*G, (g+1)*G) of q/k/v are
+ * written at  base + g*group_stride + ((h % G)*(Na+Nb) + n)*128  (elements), so that with
+ * q = buf, k = buf + G*N*128, v = buf + 2*G*N*128 and group_stride = 3*G*N*128 the buffer is
+ * [H/G][3][G][N][128]: one contiguous all-to-all chunk per destination rank.  q_pre keeps the
+ * plain [H][N][128] layout.  group_heads = 0 is ca_qkv_prep. */
+ca_status ca_qkv_prep_grouped(const void* qkv_a, int64_t row_stride_a, int Na,
+                              const void* qkv_b, int64_t row_stride_b, int Nb,
+                              const void* q_scale_a, const void* k_scale_a,
+                              const void* q_scale_b, const void* k_scale_b,
+                              const float* rope, int B, int H,
+                              void* q, void* k, void* v, void* q_pre,
+                              int group_heads, int64_t group_stride, void* stream);
 
 /* ---- K2: one-way joint attention (tcgen05 / TMEM / TMA) ---------------------
  * q,k,v bf16 [B,H,P+T+C,128], order [img|txt|concept].
@@ -177,6 +189,23 @@ ca_status ca_binary_masks(const float* heat, uint8_t* mask, int M, int P, void* 
  * (area_union = area_pred + area_lab - area_inter is left to the caller, as in the reference). */
 ca_status ca_segmentation_counts(const float* predict, const float* target, int64_t n, int nclass,
                                  uint64_t* counts, void* stream);
+
+/* ---- K7: layout kernels of the sequence-parallel exchange (multi-GPU, B = 1) ----
+ * W ranks each own Pl image rows, Tl text rows (and a replica of the C concept rows) for every
+ * token-wise op; attention runs head-split (Hl = H/W heads per rank over all rows).  An all-to-all
+ * (NCCL, caller side) moves contiguous per-rank chunks; these are the permutations around it.
+ * The reference has no multi-GPU path; K2 row order is [img | txt | concept].
+ *   ca_seq_unpack_qkv  recv [W][3][Hl][Pl+Tl+C][128] -> q,k,v [Hl][W*Pl + W*Tl + C][128]
+ *                      (concept rows from chunk `self`)
+ *   ca_seq_pack_out    K2 outputs out_img [W*Pl][Hl*128], out_txtc [W*Tl+C][Hl*128]
+ *                      -> send [W][Pl+Tl+C][Hl*128]
+ *   ca_seq_unpack_out  recv [W][Pl+Tl+C][Hl*128] -> attn_img [Pl][W*Hl*128], attn_tc [Tl+C][W*Hl*128] */
+ca_status ca_seq_unpack_qkv(const void* recv, int W, int self, int Hl, int Pl, int Tl, int C,
+                            void* q, void* k, void* v, void* stream);
+ca_status ca_seq_pack_out(const void* out_img, const void* out_txtc, int W, int Hl, int Pl, int Tl,
+                          int C, void* send, void* stream);
+ca_status ca_seq_unpack_out(const void* recv, int W, int Hl, int Pl, int Tl, int C,
+                            void* attn_img, void* attn_tc, void* stream);
 
 /* ---- host-buffer form of compute_heatmaps_from_vectors (:29-91) --------------
  * image_host  bf16 [Nt,L,B,P,K]   (or per-head [Nt,L,B,H,P,d] when per_head != 0)
