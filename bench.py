@@ -127,6 +127,8 @@ def run_ours(args, rank, world, local_rank):
     side, C, nsteps, layers = wl["side"], wl["C"], wl["nsteps"], wl["layers"]
     mode, batch = wl["mode"], wl["batch"]
     sharded = bool(wl.get("head_shard")) and world > 1
+    if args.hs_mode == "auto":
+        args.hs_mode = "sequence" if world > 2 else "tensor"
     guidance = wl.get("guidance", 0.0)
     concepts = CONCEPT_WORDS[:C]
     prompt = "A dragon standing on a rock"
@@ -383,9 +385,10 @@ def main():
     ap.add_argument("--config", default="schnell-1024", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel individually (A/B)")
-    ap.add_argument("--hs-mode", choices=("tensor", "sequence"), default="tensor",
+    ap.add_argument("--hs-mode", choices=("auto", "tensor", "sequence"), default="auto",
                     help="head-sharded workloads: tensor-parallel linears, or sequence-parallel rows "
-                         "with the head split only inside the attention")
+                         "with the head split only inside the attention; auto = sequence on more than "
+                         "2 GPUs (measured: 4.22 vs 3.19 images/s on 8, 1.22 vs 1.27 on 2)")
     ap.add_argument("--tp-overlap", action="store_true",
                     help="head-sharded mode: two token chunks on two streams around the all-reduces (A/B)")
     ap.add_argument("--no-side-stream", action="store_true", help="text stream on the main CUDA stream (A/B)")

@@ -439,18 +439,27 @@ class FluxDiTEngine:
             fn(0, mid)
             main.wait_stream(self._tp_side)
 
-        def attend(qkv_a, qkv_b, scales_a, scales_b, rope_x, n_con, amode, want_q_pre=False, out=None):
+        def attend(qkv_a, qkv_b, scales_a, scales_b, rope_x, n_con, amode, want_q_pre=False, out=None,
+                   meanwhile=None):
             """K1b + K2 -> (attn_img [B,P,*], attn_tc [B,T+n_con,*], q_pre | None) for this rank's
             rows.  Sequence-parallel: K1b writes the all-to-all send buffer, K2 runs this rank's
-            heads over ALL rows, a second all-to-all brings back every head of the local rows."""
+            heads over ALL rows, a second all-to-all brings back every head of the local rows.
+            `meanwhile()` is work that does not depend on the attention (the MLP-in GEMM of a single
+            block): it is launched while the q/k/v exchange is on NVLink."""
             if not seqpar:
+                if meanwhile is not None:
+                    meanwhile()
                 res = ops.qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope_x, Hl, want_q_pre=want_q_pre)
                 o = (None, None) if out is None else out
                 a_img, a_tc = ops.joint_attention(res[0], res[1], res[2], P, T, n_con, amode, o[0], o[1])
                 return a_img, a_tc, (res[3] if want_q_pre else None)
             send, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H,
                                                self.hs.h_local, want_q_pre=want_q_pre)
-            q, k, v = ops.seq_unpack_qkv(self.hs.all_to_all(send), rk, P, T, n_con)
+            recv, wait = self.hs.all_to_all_begin(send)
+            if meanwhile is not None:
+                meanwhile()
+            wait()
+            q, k, v = ops.seq_unpack_qkv(recv, rk, P, T, n_con)
             o_img, o_tc = ops.joint_attention(q, k, v, Pg, Tg, n_con, amode)
             back = self.hs.all_to_all(ops.seq_pack_out(o_img, o_tc, W, P, T, n_con))
             a_img, a_tc = ops.seq_unpack_out(back, P, T, n_con, out)
@@ -568,13 +577,18 @@ class FluxDiTEngine:
             pre = f"single_blocks.{i}"
             o = off(pre + ".modulation.lin")
             h = self._lin(pre + ".linear1q", xm)                                  # [B,N,3*Hl*128]
-            g = self._lin_gelu(pre + ".linear1m", xm)                             # [B,N,M/G] gelu in epilogue
+            box = {}
+
+            def mlp_in(box=box, pre=pre, xm=xm):                                  # [B,N,M/G] gelu in epilogue
+                box["g"] = self._lin_gelu(pre + ".linear1m", xm)
             scales = (self.sd[pre + ".norm.query_norm.scale"], self.sd[pre + ".norm.key_norm.scale"])
             if B == 1:
                 attn = torch.empty(1, N, Hl * 128, device=dev, dtype=BF16)
-                attend(h, None, scales, None, rope_s, 0, _cabi.ATTN_BOTH, out=(attn[:, :P], attn[:, P:]))
+                attend(h, None, scales, None, rope_s, 0, _cabi.ATTN_BOTH, out=(attn[:, :P], attn[:, P:]),
+                       meanwhile=mlp_in)
             else:
-                attn = torch.cat(attend(h, None, scales, None, rope_s, 0, _cabi.ATTN_BOTH)[:2], 1)
+                attn = torch.cat(attend(h, None, scales, None, rope_s, 0, _cabi.ATTN_BOTH, meanwhile=mlp_in)[:2], 1)
+            g = box["g"]
             last = i + 1 == p.depth_single_blocks
             on = 0 if last else off(f"single_blocks.{i + 1}.modulation.lin")
             xm_next = None if last else torch.empty_like(x)

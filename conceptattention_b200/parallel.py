@@ -201,6 +201,18 @@ class HeadShard:
         dist.all_to_all_single(out, x, group=self.group)
         return out
 
+    def all_to_all_begin(self, x: torch.Tensor):
+        """Start `all_to_all(x)` and return (out, wait): on NCCL the exchange runs on the process
+        group's own stream from here on, so whatever the caller launches before calling `wait()`
+        overlaps it; `wait()` makes the current stream wait for the data.  gloo / one rank: done
+        synchronously."""
+        if self.world == 1 or self._gloo():
+            return self.all_to_all(x), (lambda: None)
+        assert x.is_contiguous() and x.shape[0] == self.world
+        out = torch.empty_like(x)
+        work = dist.all_to_all_single(out, x, group=self.group, async_op=True)
+        return out, work.wait
+
     def all_gather_heads(self, x: torch.Tensor) -> torch.Tensor:
         """x [..., H_local*d] (this rank's heads) -> [..., H*d] with heads in rank order."""
         return self.all_gather(x, -1)

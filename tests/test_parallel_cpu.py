@@ -131,3 +131,39 @@ def test_head_shard_rejects_uneven_split():
     import pytest
     with pytest.raises(ValueError):
         HeadShard(0, 5, 24)
+
+
+def _seq_job(rank, world):
+    """Sequence-parallel exchange on CPU: local rows x all heads -> all-to-all -> local heads x all
+    rows -> attention -> all-to-all back -> local rows x all heads (K7's permutations in plain torch)."""
+    import torch.nn.functional as F
+    H, d, Pl, Tl = 4, 16, 6, 2
+    W, Hl, Nl = world, H // world, Pl + Tl
+    hs = HeadShard(rank, world, H, sequence_parallel=True)
+    g = torch.Generator().manual_seed(1)
+    # full problem in K2 row order [img (W*Pl) | txt (W*Tl)], bf16 like the device path
+    qkv = torch.randn(3, H, W * Nl, d, generator=g).to(torch.bfloat16)
+    rows = torch.cat((torch.arange(rank * Pl, (rank + 1) * Pl), W * Pl + torch.arange(rank * Tl, (rank + 1) * Tl)))
+    local = qkv[:, :, rows]                                            # [3,H,Nl,d] what this rank computed
+    send = local.view(3, W, Hl, Nl, d).permute(1, 0, 2, 3, 4).contiguous()   # [W,3,Hl,Nl,d]
+    recv = hs.all_to_all(send)
+    recv2, wait = hs.all_to_all_begin(send)
+    wait()
+    ok_begin = torch.equal(recv, recv2)
+    full_rows = torch.cat([torch.cat((torch.arange(w * Pl, (w + 1) * Pl), W * Pl + torch.arange(w * Tl, (w + 1) * Tl)))
+                           for w in range(W)])
+    mine = torch.empty(3, Hl, W * Nl, d, dtype=torch.bfloat16)
+    mine[:, :, full_rows] = recv.permute(1, 2, 0, 3, 4).reshape(3, Hl, W * Nl, d)
+    ok_qkv = torch.equal(mine, qkv[:, rank * Hl:(rank + 1) * Hl])
+    out = F.scaled_dot_product_attention(mine[0].float(), mine[1].float(), mine[2].float())      # [Hl,N,d]
+    back = out[:, full_rows].view(Hl, W, Nl, d).permute(1, 2, 0, 3).contiguous()                 # [W,Nl,Hl,d]
+    got = hs.all_to_all(back).permute(1, 0, 2, 3).reshape(Nl, H * d)                             # rows x all heads
+    ref = F.scaled_dot_product_attention(qkv[0].float(), qkv[1].float(), qkv[2].float())         # [H,N,d]
+    ok_out = torch.equal(got, ref[:, rows].permute(1, 0, 2).reshape(Nl, H * d))
+    return ok_begin, ok_qkv, ok_out
+
+
+def test_sequence_parallel_exchange_round_trip():
+    ret = _run(_seq_job)
+    for r in (0, 1):
+        assert ret[r] == (True, True, True), (r, ret[r])
