@@ -212,9 +212,10 @@ class FluxDiTEngine:
         self.use_graphs = True
         # the text+concept stream of a double block (five small, latency-bound launches per
         # GEMM pair) runs on a second CUDA stream beside the image stream; captured graphs keep
-        # the fork/join as parallel branches.  Off in the head-sharded mode (one NCCL
+        # the fork/join as parallel branches.  Off in the tensor-parallel head-sharded mode (one NCCL
         # communicator must see its collectives from one stream).
-        self.use_side_stream = head_shard is None or head_shard.world == 1
+        self.use_side_stream = (head_shard is None or head_shard.world == 1
+                                or head_shard.sequence_parallel)   # its text chain has no collective
         self.skip_unused_tail = True      # see the double-block loop (encode path only)
         # head-sharded mode: two token chunks on two streams so one chunk computes while the other's
         # partial sums are in the all-reduce.  Measured on 8 GPUs (config 5): 315 -> 353 ms per image
@@ -415,7 +416,7 @@ class FluxDiTEngine:
         ln = {"img": ops.ln_modulate(x_img, m_vec, None, None, o_i, o_i + D),
               "txt": ops.ln_modulate(txtc, m_vec, m_con, T, o_t, o_t + D)}
         side = None
-        if self.use_side_stream and not sharded:
+        if self.use_side_stream and not tp:
             if self._side is None:
                 self._side = torch.cuda.Stream(device=dev)
             side = self._side
