@@ -160,9 +160,11 @@ class FluxDiTEngine:
     (see weights.linear_shapes); tensors must be bf16 on `device`."""
 
     def __init__(self, params: FluxParams, state_dict: dict, device="cuda:0", head_shard=None):
-        """`head_shard` (parallel.HeadShard): this rank computes only its head slice of the
-        double-stream attention (qkv GEMM rows, K1b, K2, K3 partial logits); attention
-        outputs are all-gathered over heads, partial heatmap logits all-reduced."""
+        """`head_shard` (parallel.HeadShard, one image over several GPUs):
+        tensor-parallel form - this rank's head slice of every attention (qkv rows, K1b, K2, K3
+        partial logits), linears sharded around it, partial sums and partial heatmap logits
+        all-reduced; `sequence_parallel=True` - whole weights, this rank's 1/world of the rows
+        for every token-wise op, heads split only inside the attention (two all-to-alls)."""
         self.p = params
         self.device = torch.device(device)
         self.hs = head_shard
