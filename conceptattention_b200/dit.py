@@ -290,6 +290,22 @@ class FluxDiTEngine:
             self._rope_cache.update(key=key, ids=parts, table=tables[digest])
         return self._rope_cache["table"]
 
+    def _rope_local(self, rope, P, T):
+        """Sequence-parallel mode: this rank's rows [img_l | txt_l | concept] of the full table
+        (rows [img P | txt T | concept]).  One table per (full table, P, T), kept beside the full
+        table it was cut from, so its address is as stable as the full table's (captured graphs
+        bake it in; `_capture` also holds a reference)."""
+        W, rk = self.hs.world, self.hs.rank
+        key = (rope.data_ptr(), P, T)
+        local = self._rope_cache.setdefault("locals", {})
+        if key not in local:
+            if len(local) >= 16:
+                local.pop(next(iter(local)))
+            Pl, Tl = P // W, T // W
+            local[key] = (rope, torch.cat((rope[rk * Pl:(rk + 1) * Pl], rope[P + rk * Tl:P + (rk + 1) * Tl],
+                                           rope[P + T:]), 0).contiguous())
+        return local[key][1]
+
     # -- forward -----------------------------------------------------------------------
     @torch.no_grad()
     def forward(self, img, img_ids, txt, txt_ids, concepts, concept_ids, concept_vec, timesteps, y,
@@ -317,6 +333,10 @@ class FluxDiTEngine:
         if not self.p.guidance_embed:
             args["guidance"] = None
         rope = self._rope(img_ids, txt_ids, concept_ids)
+        seqpar = self.hs is not None and self.hs.world > 1 and self.hs.sequence_parallel
+        if seqpar and img.shape[1] % self.hs.world == 0 and txt.shape[1] % self.hs.world == 0:
+            # cut this rank's rows of the table OUTSIDE any capture (stable address, eager memory)
+            self._rope_local(rope, img.shape[1], txt.shape[1])
         key = (tuple((k, tuple(v.shape)) for k, v in args.items() if v is not None),
                attention_mode(joint_attention_kwargs), bool(stop_after_multimodal_attentions),
                rope.data_ptr(), accumulator.signature(self.p.depth) if accumulator is not None else None)
@@ -351,8 +371,9 @@ class FluxDiTEngine:
         with torch.cuda.graph(graph, pool=self._graph_pool):
             pred, _ = self._forward(**{k: static.get(k) for k in args}, **rest)
         acc = rest["accumulator"]
+        local = self._rope_cache.get("locals", {}).get((rope.data_ptr(), args["img"].shape[1], args["txt"].shape[1]))
         return {"graph": graph, "static": static, "pred": pred, "n_launch": ops.LAUNCHES - n0,
-                "keep": (rope, None if acc is None else acc.acc)}
+                "keep": (rope, local, None if acc is None else acc.acc)}
 
     @torch.no_grad()
     def _forward(self, img, img_ids, txt, txt_ids, concepts, concept_ids, concept_vec, timesteps, y,
@@ -392,11 +413,7 @@ class FluxDiTEngine:
                 raise ValueError(f"sequence-parallel mode needs B = 1 and P, T divisible by {W} (got {B}, {P}, {T})")
             Pg, Tg, P, T = P, T, P // W, T // W
             img, txt = img[:, rk * P:(rk + 1) * P], txt[:, rk * T:(rk + 1) * T]
-            if self._rope_cache.get("local_key") != (rope.data_ptr(), W, rk, P, T):
-                self._rope_cache["local"] = torch.cat(
-                    (rope[rk * P:(rk + 1) * P], rope[Pg + rk * T:Pg + (rk + 1) * T], rope[Pg + Tg:]), 0).contiguous()
-                self._rope_cache["local_key"] = (rope.data_ptr(), W, rk, P, T)
-            rope = self._rope_cache["local"]                 # rows [img_l | txt_l | concept]
+            rope = self._rope_local(rope, Pg, Tg)            # rows [img_l | txt_l | concept]
         x_img = self._lin("img_in", img).contiguous()
         vec, cvec = cond(y), cond(concept_vec)
         txtc = self._lin("txt_in", torch.cat((txt, concepts), 1)).contiguous()   # [B,T+C,D]
