@@ -944,6 +944,382 @@ attn_v1_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
+// =============================================================================
+// Persistent form of v3 (impl 14, EXPERIMENTAL: opt-in through ca_debug_set_attention_impl).
+// One CTA per SM walks the flat unit list [concept | whole | stream-K pieces] with a static
+// stride; TMEM is allocated and the barriers are initialised once.  All mbarrier parities come
+// from running counters (K/V ring items, per-tile S/P completions, units) instead of `j & 1`.
+// What this buys: the next unit's Q/K/V loads and its first QK^T run under the
+// current unit's epilogue, and the per-CTA start-up (TMEM alloc, barrier init, tensor-map
+// prefetch, first TMA round trip) is paid once per SM instead of once per unit.
+// Ordering that makes it safe without an "O free" barrier: the first PV of unit n+1 needs
+// p_full, which all eight softmax warps arrive on only after their epilogue of unit n has read O
+// out of TMEM; the next unit's QK^T overwrites S/P only behind the last PV in the tensor pipe's
+// issue order.  One new barrier, q_empty (MMA warp -> producer): the unit's last QK^T, the last
+// reader of sm.q, has been committed.
+// =============================================================================
+struct SmemP : SmemV1 {
+  uint64_t q_empty;
+  float sk_flag[4];
+};
+
+__device__ __forceinline__ void pz_producer(SmemP& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
+                                            const CUtensorMap* tmv, const AttnParams& p, int total) {
+  int item = 0, n_unit = 0;
+  for (int cta = blockIdx.x; cta < total; cta += gridDim.x) {
+    const UnitV1 u = decode_unit(p, cta);
+    if (u.n_local == 0) continue;
+    const int bh = u.bh;
+    auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
+      mbar_expect_tx(bar, kTileBytes);
+      tma_load_3d(dst, tm, bar, 0, row0, bh);
+      tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+    };
+    auto load_kv = [&](const CUtensorMap* tm, int j) {
+      int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+      const int slot = item % kKvStages;
+      mbar_wait(&sm.kv_empty[slot], ((item / kKvStages) & 1) ^ 1);
+      load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+      ++item;
+    };
+    if (n_unit > 0) mbar_wait(&sm.q_empty, (n_unit - 1) & 1);   // previous unit's QK^Ts are done with sm.q
+    load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
+    load_kv(tmk, 0);
+    if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
+    load_kv(tmv, 0);
+    for (int j = 1; j < u.n_local; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
+    ++n_unit;
+  }
+}
+
+__device__ __forceinline__ void pz_mma(SmemP& sm, uint32_t tmem, const AttnParams& p, int total) {
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  int item = 0;                       // K/V ring items consumed before this unit
+  int n_qf[2] = {0, 0};               // q_full[t] completions consumed
+  int n_pf[2] = {0, 0};               // p_full[t] completions consumed
+  auto kv_wait = [&](int it) {
+    const int slot = it % kKvStages;
+    mbar_wait(&sm.kv_full[slot], (it / kKvStages) & 1);
+    return slot;
+  };
+  auto qk = [&](int t, int kslot) {                      // S_t = Q_t K^T
+    const uint32_t qa = smem_u32(sm.q[t]), ka = smem_u32(sm.kv[kslot]);
+#pragma unroll
+    for (int kk = 0; kk < kD / 16; ++kk) {
+      const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+      mma_ss(tmem + t * 128, make_smem_desc(qa + off, 16, 1024), make_smem_desc(ka + off, 16, 1024),
+             idesc_qk, kk > 0);
+    }
+    mma_commit(&sm.s_full[t]);
+  };
+  auto pv = [&](int t, int vslot, bool acc) {            // O_t (+)= P_t V, P_t from TMEM
+    const uint32_t va = smem_u32(sm.kv[vslot]);
+#pragma unroll
+    for (int kk = 0; kk < kBN / 16; ++kk)
+      mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kk * 8,
+             make_smem_desc(va + kk * 2048, kHalfBytes, 1024), idesc_pv, acc || kk > 0);
+  };
+  for (int cta = blockIdx.x; cta < total; cta += gridDim.x) {
+    const UnitV1 u = decode_unit(p, cta);
+    if (u.n_local == 0) continue;
+    const bool two = u.n_q == 2;
+    mbar_wait(&sm.q_full[0], n_qf[0]++ & 1);
+    int ks = kv_wait(item);
+    tc_fence_after();
+    qk(0, ks);
+    if (two) { mbar_wait(&sm.q_full[1], n_qf[1]++ & 1); tc_fence_after(); qk(1, ks); }
+    mma_commit(&sm.kv_empty[ks]);
+    if (u.n_local == 1) mma_commit(&sm.q_empty);
+    for (int j = 0; j < u.n_local; ++j) {
+      const bool has_next = j + 1 < u.n_local;
+      const int vs = kv_wait(item + 2 * j + 1);
+      if (has_next) ks = kv_wait(item + 2 * j + 2);
+      mbar_wait(&sm.p_full[0], n_pf[0]++ & 1);
+      tc_fence_after();
+      pv(0, vs, j > 0);
+      if (has_next) qk(0, ks);
+      if (two) {
+        mbar_wait(&sm.p_full[1], n_pf[1]++ & 1);
+        tc_fence_after();
+        pv(1, vs, j > 0);
+      }
+      mma_commit(&sm.kv_empty[vs]);
+      if (has_next) {
+        if (two) qk(1, ks);
+        mma_commit(&sm.kv_empty[ks]);
+        if (j + 2 == u.n_local) mma_commit(&sm.q_empty);   // that was the unit's last QK^T
+      }
+    }
+    mma_commit(&sm.o_done);
+    item += 2 * u.n_local;
+  }
+}
+
+template <int kPolyEvery>
+__device__ __forceinline__ void pz_softmax(SmemP& sm, uint32_t tmem, const AttnParams& p, int half,
+                                           int total) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const float scale = p.scale_log2;
+  const int c0 = half * 64;
+  uint32_t use = 0;                                       // exchange-buffer parity (runs across units)
+  int n_sf[2] = {0, 0};                                   // s_full[t] completions consumed
+  int n_unit = 0;                                         // o_done completions consumed
+
+  auto mask_chunk = [&](uint32_t* r, int cbase, int valid) {
+    if (valid < kBN) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) if (cbase + i >= valid) r[i] = 0xff800000u;   // -inf
+    }
+  };
+  auto max_chunk = [&](const uint32_t* r, float mx) {
+    float m0 = __uint_as_float(r[0]), m1 = __uint_as_float(r[1]);
+#pragma unroll
+    for (int i = 2; i < 32; i += 2) {
+      m0 = fmaxf(m0, __uint_as_float(r[i])); m1 = fmaxf(m1, __uint_as_float(r[i + 1]));
+    }
+    return fmaxf(mx, fmaxf(m0, m1));
+  };
+  auto exchange = [&](float mine, bool take_max) {        // combine with the row's other thread
+    float* xb = &sm.xchg[0][use & 1][0][0];
+    xb[half * kBM + row] = mine;
+    softmax_bar_sync(1);
+    const float other = xb[(half ^ 1) * kBM + row];
+    ++use;
+    return take_max ? fmaxf(mine, other) : mine + other;
+  };
+
+#pragma unroll 1
+  for (int cta = blockIdx.x; cta < total; cta += gridDim.x) {
+    const UnitV1 u = decode_unit(p, cta);
+    if (u.n_local == 0) continue;
+    const int b = u.bh / p.H, h = u.bh - b * p.H;
+    float m_used[2] = {-INFINITY, -INFINITY}, l_sum[2] = {0.f, 0.f};
+
+#pragma unroll 1
+    for (int j = 0; j < u.n_local; ++j) {
+      int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (t < u.n_q) {
+          const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
+          mbar_wait(&sm.s_full[t], n_sf[t]++ & 1);
+          tc_fence_after();
+          uint32_t ra[32], rb[32];
+          tmem_ld32(t_s + c0, ra);
+          tmem_ld32(t_s + c0 + 32, rb);
+          tmem_wait_ld32(ra);
+          tmem_wait_ld32(rb);
+          mask_chunk(ra, c0, valid);
+          mask_chunk(rb, c0 + 32, valid);
+          const float m_loc = max_chunk(rb, max_chunk(ra, -INFINITY));
+          auto exp_regs = [&](const uint32_t* r, float m_ref, uint32_t* pk, uint64_t& rs2) {
+            const float mb = m_ref * scale;
+            const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const uint64_t x2 = fma2(pk64(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])), scale2, nmb2);
+              float e0, e1;
+              if (use_poly<kPolyEvery>(i)) {
+                exp2_poly2(x2, e0, e1);
+              } else {
+                float x0, x1;
+                upk64(x2, x0, x1);
+                e0 = ex2(x0); e1 = ex2(x1);
+              }
+              rs2 = add2(rs2, pk64(e0, e1));
+              pk[i] = pack2(e0, e1);
+            }
+          };
+          auto rescale_o = [&](float alpha) {
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 8) {
+              uint32_t rc[8];
+              tmem_ld8(t_o + c0 + c, rc);
+              tmem_wait_ld8(rc);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+              tmem_st8(t_o + c0 + c, rc);
+            }
+          };
+          uint32_t pka[16], pkb[16];
+          uint64_t rs2 = pk64(0.f, 0.f);
+          const float mx = exchange(m_loc, true);
+          const bool grow = (mx - m_used[t]) * scale > kRescaleThreshold;   // true on the first tile
+          const float m_new = grow ? mx : m_used[t];
+          if (j > 0 && __any_sync(0xffffffffu, grow)) {
+            const float alpha = grow ? ex2((m_used[t] - m_new) * scale) : 1.f;
+            l_sum[t] *= alpha;
+            rescale_o(alpha);
+          }
+          m_used[t] = m_new;
+          exp_regs(ra, m_new, pka, rs2);
+          exp_regs(rb, m_new, pkb, rs2);
+          tmem_st16(t_s + half * 32, pka);
+          tmem_st16(t_s + half * 32 + 16, pkb);
+          float r0, r1;
+          upk64(rs2, r0, r1);
+          l_sum[t] += r0 + r1;
+          tmem_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.p_full[t]);
+        }
+      }
+    }
+
+    // ---- epilogue of the unit -----------------------------------------------------------
+    mbar_wait(&sm.o_done, n_unit++ & 1);
+    tc_fence_after();
+    if (u.part_slot < 0) {
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (t < u.n_q) {
+          const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
+          const float inv_l = 1.f / exchange(l_sum[t], false);
+          const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+#pragma unroll
+          for (int c = 0; c < 64; c += 32) {
+            uint32_t r[32];
+            tmem_ld32(t_o + c0 + c, r);
+            tmem_wait_ld32(r);
+            if (row < q_rows) {
+              float o[32];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+              store_out_row(p, b, h, q_row0 + row, o, inv_l, c0 + c, 32);
+            }
+          }
+        }
+      }
+      continue;
+    }
+
+    // ---- stream-K piece: partial to its slot, last arriver merges (as in v3_softmax) -------
+    const int n_main = p.n_main_tiles;
+    {
+      float* slot = p.ws_part + (size_t)u.part_slot * kPartFloats;
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (t < u.n_q) {
+          const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
+          float* pt = slot + t * kPartTile;
+          const float l_tot = exchange(l_sum[t], false);
+          if (half == 0) { pt[kBM * kD + row] = m_used[t]; pt[kBM * kD + kBM + row] = l_tot; }
+#pragma unroll
+          for (int c = 0; c < 64; c += 32) {
+            uint32_t r[32];
+            tmem_ld32(t_o + c0 + c, r);
+            tmem_wait_ld32(r);
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              *reinterpret_cast<uint4*>(pt + (((c0 + c + i) >> 2) * kBM + row) * 4) =
+                  make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+          }
+        }
+      }
+    }
+    const int64_t u_lo = (int64_t)u.sk_unit * n_main, u_hi = u_lo + n_main;
+    const int64_t total_steps = (int64_t)p.sk_units * n_main;
+    const int i_first = (int)((u_lo * p.sk_sms) / total_steps);
+    int n_pieces = 0;
+    for (int i = max(0, i_first - 1); i < p.sk_sms; ++i) {
+      int64_t lo, hi;
+      sk_range(p, n_main, i, lo, hi);
+      if (lo >= u_hi) break;
+      if (hi > u_lo && hi > lo) ++n_pieces;
+    }
+    __threadfence();
+    softmax_bar_sync(1);
+    if (threadIdx.x == 128) {                               // first softmax thread
+      const int ticket = atomicAdd(p.ws_count + u.sk_unit, 1);
+      sm.sk_flag[0] = ticket == n_pieces - 1 ? 1.f : 0.f;
+    }
+    softmax_bar_sync(1);
+    const bool merge = sm.sk_flag[0] != 0.f;
+    softmax_bar_sync(1);                                    // flag read by all before the next piece rewrites it
+    if (!merge) continue;
+    __threadfence();
+#pragma unroll 1
+    for (int t = 0; t < 2; ++t) {
+      if (t >= u.n_q) break;
+      const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+      float m_all = -INFINITY;
+      for (int i = max(0, i_first - 1); i < p.sk_sms; ++i) {
+        int64_t lo, hi;
+        sk_range(p, n_main, i, lo, hi);
+        if (lo >= u_hi) break;
+        if (!(hi > u_lo && hi > lo)) continue;
+        const int k = (lo / n_main == u.sk_unit) ? 0 : 1;
+        const float* pt = p.ws_part + (size_t)(2 * i + k) * kPartFloats + t * kPartTile;
+        m_all = fmaxf(m_all, __ldcg(pt + kBM * kD + row));
+      }
+#pragma unroll 1
+      for (int c = 0; c < 64; c += 32) {
+        float acc[32], l_all = 0.f;
+#pragma unroll
+        for (int e = 0; e < 32; ++e) acc[e] = 0.f;
+        for (int i = max(0, i_first - 1); i < p.sk_sms; ++i) {
+          int64_t lo, hi;
+          sk_range(p, n_main, i, lo, hi);
+          if (lo >= u_hi) break;
+          if (!(hi > u_lo && hi > lo)) continue;
+          const int k = (lo / n_main == u.sk_unit) ? 0 : 1;
+          const float* pt = p.ws_part + (size_t)(2 * i + k) * kPartFloats + t * kPartTile;
+          const float f = ex2((__ldcg(pt + kBM * kD + row) - m_all) * scale);
+          l_all += f * __ldcg(pt + kBM * kD + kBM + row);
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            const float4 o4 = __ldcg(reinterpret_cast<const float4*>(pt + (((c0 + c + e) >> 2) * kBM + row) * 4));
+            acc[e] += f * o4.x; acc[e + 1] += f * o4.y; acc[e + 2] += f * o4.z; acc[e + 3] += f * o4.w;
+          }
+        }
+        if (row < q_rows) store_out_row(p, b, h, q_row0 + row, acc, 1.f / l_all, c0 + c, 32);
+      }
+    }
+    if (threadIdx.x == 128) p.ws_count[u.sk_unit] = 0;      // ready for the next launch
+  }
+}
+
+template <int kPolyEvery>
+__global__ void __launch_bounds__(384, 1)
+attn_persist_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+                    const __grid_constant__ CUtensorMap tmv, const AttnParams p, const int total) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemP& sm = *reinterpret_cast<SmemP*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
+    for (int i = 0; i < kKvStages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.s_full[i], 1); mbar_init(&sm.p_full[i], 8); }
+    mbar_init(&sm.o_done, 1);
+    mbar_init(&sm.q_empty, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+  if (warp < 4) {
+    setmaxnreg_dec<96>();
+    if (warp == 0) {
+      if (elect_one()) pz_producer(sm, &tmq, &tmk, &tmv, p, total);
+    } else if (warp == 1) {
+      if (elect_one()) pz_mma(sm, tmem, p, total);
+    }
+  } else {
+    setmaxnreg_inc<200>();
+    pz_softmax<kPolyEvery>(sm, tmem, p, (warp >> 2) - 1, total);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
 // CA_ATTN_NEITHER: concept_attn = concept_v  (modified_double_stream_block.py:157-159),
 // i.e. a head-merge copy of the concept rows of V.
 __global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnParams p) {
@@ -1021,7 +1397,18 @@ static SkPlan plan_streamk(int W, int n_concept, int n_steps, bool allowed) {
 
 static bool impl_is_v3() {
   return g_attention_impl == 0 || g_attention_impl == 4 || g_attention_impl == 5 || g_attention_impl == 10 ||
-         g_attention_impl == 13;
+         g_attention_impl == 13 || g_attention_impl == 14;
+}
+
+static int sm_count_cached() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      n = 0;
+  }
+  return n;
 }
 
 }  // namespace ca
@@ -1093,7 +1480,16 @@ extern "C" ca_status ca_joint_attention_ws(const void* q, const void* k, const v
     }
     const int64_t ctas = (int64_t)p.n_dp + 2 * p.sk_sms + p.n_concept;
     if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
-    if (ctas > 0) {
+    if (ctas > 0 && g_attention_impl == 14) {
+      // experimental persistent v3: one CTA per SM walks the same flat unit list
+      const int sms = sm_count_cached();
+      if (sms <= 0) return CA_ERR_CUDA;
+      const int smem = (int)sizeof(SmemP) + 1024;
+      auto kern = attn_persist_kernel<4>;
+      CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      kern<<<(unsigned)(ctas < sms ? ctas : sms), 384, smem, st>>>(tmq, tmk, tmv, p, (int)ctas);
+      CA_LAUNCH_CHECK();
+    } else if (ctas > 0) {
       const int smem = (int)sizeof(SmemV1) + 1024;
       // impl 0: v3 (two cooperating warpgroups), polynomial exp2 on every 4th element pair;
       // 4 / 5: v3 every 2nd pair / all MUFU; 2 / 3: v2 (one warpgroup per tile) all MUFU / every 4th;

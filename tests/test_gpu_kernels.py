@@ -232,6 +232,31 @@ def test_joint_attention_optimistic_max_is_bit_identical(ops, B, H, P, T, C, mod
     close(outs[13][0] if False else ops.joint_attention(q, k, v, P, T, C, mode)[0], ri, rtol=2e-2, atol=1e-2)
 
 
+@pytest.mark.parametrize("B,H,P,T,C,mode,plan", [(1, 1, 200, 100, 1, 0, 0), (1, 2, 144, 72, 3, 1, 0),
+                                                 (2, 24, 1024, 256, 4, 0, 0), (1, 2, 2000, 200, 3, 0, 7),
+                                                 (1, 2, 2200, 200, 5, 0, 24)])
+def test_joint_attention_persistent_form_is_bit_identical(ops, B, H, P, T, C, mode, plan):
+    """impl 14 (opt-in): one CTA per SM walks the same unit list with running barrier parities; the
+    per-unit maths and the stream-K merge order are unchanged, so outputs must equal the default
+    kernel's bit for bit — with fewer units than SMs, several units per SM (2 x 24 heads x 5 pairs
+    + 48 concept units on 148 SMs) and forced stream-K plans."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    N = P + T + C
+    q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((50, 1.5), (51, 1.0), (52, 1.0)))
+    outs = {}
+    lib.ca_debug_set_attention_streamk(plan)
+    try:
+        for impl in (0, 14):
+            lib.ca_debug_set_attention_impl(impl)
+            outs[impl] = ops.joint_attention(q, k, v, P, T, C, mode)
+            torch.cuda.synchronize()
+    finally:
+        lib.ca_debug_set_attention_impl(0)
+        lib.ca_debug_set_attention_streamk(0)
+    assert torch.equal(outs[0][0], outs[14][0]) and torch.equal(outs[0][1], outs[14][1])
+
+
 def test_joint_attention_one_way(ops):
     """Image and text rows must not depend on the concept tokens at all (bit-exact)."""
     B, H, P, T, C = 1, 2, 384, 128, 5
