@@ -77,6 +77,10 @@ def load():
     lib.ca_debug_set_attention_impl.restype = None
     lib.ca_debug_set_attention_streamk.argtypes = [_i]
     lib.ca_debug_set_attention_streamk.restype = None
+    lib.ca_debug_plan_streamk.argtypes = [_i, _i, _i, _i, _i, _p]
+    lib.ca_debug_plan_streamk.restype = None
+    lib.ca_debug_streamk_piece.argtypes = [_i, _i, _i, _i, _i, _p]
+    lib.ca_debug_streamk_piece.restype = _i
     lib.ca_debug_set_ln_impl.argtypes = [_i]
     lib.ca_debug_set_ln_impl.restype = None
     lib.ca_debug_set_heatmap_impl.argtypes = [_i]

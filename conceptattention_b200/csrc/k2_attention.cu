@@ -307,13 +307,13 @@ struct UnitV1 {
 };
 
 // tail range i covers key steps [lo, hi) of the concatenated tail units (n steps each)
-__device__ __forceinline__ void sk_range(const AttnParams& p, int n, int i, int64_t& lo, int64_t& hi) {
+__host__ __device__ __forceinline__ void sk_range(const AttnParams& p, int n, int i, int64_t& lo, int64_t& hi) {
   const int64_t total = (int64_t)p.sk_units * n;
   lo = (int64_t)i * total / p.sk_sms;
   hi = (int64_t)(i + 1) * total / p.sk_sms;
 }
 // piece k (0/1) of range i: [lo, hi) clipped to the first / second unit it touches
-__device__ __forceinline__ bool sk_piece(const AttnParams& p, int n, int i, int k, int& unit,
+__host__ __device__ __forceinline__ bool sk_piece(const AttnParams& p, int n, int i, int k, int& unit,
                                          int& j_begin, int& n_local) {
   int64_t lo, hi;
   sk_range(p, n, i, lo, hi);
@@ -1362,6 +1362,8 @@ int g_attention_streamk = 0; // 0 = auto (real SM count), -1 = never split, n > 
 // at most two units -> two CTAs per range, pieces of a unit merged by the last one to finish).
 struct SkPlan { int n_dp, sk_units, sk_sms; };
 
+static SkPlan plan_streamk_core(int W, int n_concept, int n_steps, int S, bool auto_rules);
+
 static SkPlan plan_streamk(int W, int n_concept, int n_steps, bool allowed) {
   SkPlan pl{W, 0, 0};
   if (!allowed || g_attention_streamk < 0 || W == 0) return pl;
@@ -1376,6 +1378,13 @@ static SkPlan plan_streamk(int W, int n_concept, int n_steps, bool allowed) {
     }
     S = sm_count;
   }
+  return plan_streamk_core(W, n_concept, n_steps, S, g_attention_streamk == 0);
+}
+
+// pure arithmetic (no device, no globals): S = SMs planned for, auto_rules = the measured thresholds
+static SkPlan plan_streamk_core(int W, int n_concept, int n_steps, int S, bool auto_rules) {
+  SkPlan pl{W, 0, 0};
+  if (W <= 0 || S <= 0) return pl;
   // the concept units (one CTA each, launched first) count towards the whole waves
   const int whole = ((W + n_concept) / S) * S - n_concept;      // main units that run unsplit
   const int R = whole >= 0 ? W - whole : W;
@@ -1390,7 +1399,7 @@ static SkPlan plan_streamk(int W, int n_concept, int n_steps, bool allowed) {
   // In test mode (planned SM count given) only the structural limits apply.
   const int64_t saved = (int64_t)(S - R) * n_steps / S;
   if ((int64_t)R * n_steps / S < 4) return pl;
-  if (g_attention_streamk == 0 && (2 * R > S || saved < 24)) return pl;
+  if (auto_rules && (2 * R > S || saved < 24)) return pl;
   pl.n_dp = W - R; pl.sk_units = R; pl.sk_sms = S;
   return pl;
 }
@@ -1415,6 +1424,21 @@ static int sm_count_cached() {
 
 extern "C" void ca_debug_set_attention_impl(int impl) { ca::g_attention_impl = impl; }
 extern "C" void ca_debug_set_attention_streamk(int sms) { ca::g_attention_streamk = sms; }
+
+// Host-only views of the stream-K arithmetic for the CPU tests (no CUDA call inside).
+// plan: out = {n_dp, sk_units, sk_sms};  piece: out = {unit, j_begin, n_local}, returns 0 for an empty piece.
+extern "C" void ca_debug_plan_streamk(int W, int n_concept, int n_steps, int sms, int auto_rules, int* out) {
+  const ca::SkPlan pl = ca::plan_streamk_core(W, n_concept, n_steps, sms, auto_rules != 0);
+  out[0] = pl.n_dp; out[1] = pl.sk_units; out[2] = pl.sk_sms;
+}
+extern "C" int ca_debug_streamk_piece(int n_steps, int sk_units, int sk_sms, int i, int k, int* out) {
+  ca::AttnParams p{};
+  p.sk_units = sk_units; p.sk_sms = sk_sms;
+  int unit = 0, j_begin = 0, n_local = 0;
+  const bool ok = ca::sk_piece(p, n_steps, i, k, unit, j_begin, n_local);
+  out[0] = unit; out[1] = j_begin; out[2] = n_local;
+  return ok ? 1 : 0;
+}
 
 extern "C" size_t ca_joint_attention_workspace_bytes(int B, int H, int P, int T, int C, int mode) {
   using namespace ca;
