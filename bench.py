@@ -16,8 +16,13 @@ roofline: the fused joint-attention kernel (K2), timed live with CUDA events aro
           every launch of the timed region, against the measured bf16 peak.
 N > 1   : one process per GPU, each generates its own images (data parallel, no
           collective on the path); NCCL is used for the barrier / max-over-ranks only.
---impl reference : the CPU oracle (port of the reference's PyTorch path; the reference
-          itself is Python and does not travel) on all host cores, bounded sample.
+roofline_hbm : K1a / K1b / K1c / K3+K4, each launch of the timed region bracketed by CUDA events
+          on its stream, algorithmic bytes / time against the measured copy bandwidth.
+gpu_reference (N = 1): the reference's OWN modules (oracle/_ref) in bf16 on the same GPU, the full
+          workload image through its denoise + compute_heatmaps_from_vectors — the real bar.
+other_configs : the other BASELINE.json configurations measured in the same run (short).
+--impl reference : the reference's own modules (oracle/_ref; the oracle port if absent) in fp32
+          on all host cores, bounded sample of the workload.
 """
 import argparse
 import json
@@ -117,9 +122,8 @@ def attention_flops(P, T, C, H, double):
     return f + (4 * D_HEAD * H * C * (C + P) if double else 0)
 
 
-def run_ours(args, rank, world, local_rank):
+def run_ours(args, rank, world, local_rank, secondary=False):
     from conceptattention_b200 import ConceptAttentionFluxPipeline, ops, sampling
-    from conceptattention_b200.dit import HeatmapAccumulator
     from conceptattention_b200.parallel import HeadShard, gather_results
     wl = WORKLOADS[args.config]
     dev = torch.device("cuda", local_rank)
@@ -138,17 +142,23 @@ def run_ours(args, rank, world, local_rank):
         from conceptattention_b200.weights import CONFIGS
         hs = HeadShard(rank, world, CONFIGS[wl["model"]].num_heads,
                        sequence_parallel=args.hs_mode == "sequence")
-    pipe = ConceptAttentionFluxPipeline(model_name=wl["model"], device=dev, seed=0 if sharded else rank,
-                                        head_shard=hs)
+    from conceptattention_b200.weights import CONFIGS, init_state_dict
+    # random-init weights with the reference's keys, drawn on the device; the same tensors are
+    # handed to the reference modules of the gpu_reference arm (shared storage)
+    sd = init_state_dict(CONFIGS[wl["model"]], seed=0 if sharded else rank, device=dev, dtype=torch.bfloat16)
+    pipe = ConceptAttentionFluxPipeline(model_name=wl["model"], device=dev, state_dict=dict(sd), head_shard=hs)
+    want_gpu_ref = (world == 1 and mode == "generate" and not args.no_gpu_reference and not secondary)
+    if not want_gpu_ref:
+        del sd
     gen = pipe.flux_generator
     pm = gen.params
-    # text encoders on the HOST (pinned) so the e2e arm pays the H2D copy of their outputs
-    host_t5 = sampling.SyntheticEmbedder(pm.context_in_dim, gen.t5.max_length, "cpu")
-    host_clip = sampling.SyntheticEmbedder(pm.vec_in_dim, None, "cpu")
+    # text encoders on the HOST (pinned cache, pinned stacking buffers) so the e2e arm pays an
+    # asynchronous H2D copy of their outputs
+    host_t5 = sampling.SyntheticEmbedder(pm.context_in_dim, gen.t5.max_length, "cpu", pin=True)
+    host_clip = sampling.SyntheticEmbedder(pm.vec_in_dim, None, "cpu", pin=True)
     for e, texts in ((host_t5, [prompt, ""] + concepts), (host_clip, [prompt, "", " ".join(concepts)])):
         for t in texts:
             e(t)
-        e._cache = {k: v.pin_memory() for k, v in e._cache.items()}
     seed0 = 0 if sharded else 1000 * rank
     host_lat = [torch.randn(batch, 16, side // 8, side // 8, generator=torch.Generator().manual_seed(seed0 + i))
                 .to(torch.bfloat16).pin_memory() for i in range(args.steps + args.warmup)]
@@ -166,11 +176,8 @@ def run_ours(args, rank, world, local_rank):
         inps = [gen.prepare_inputs(prompt, concepts, l) for l in dev_lat]
 
         def device_step(i):
-            if wl.get("per_pair"):
-                acc = HeatmapAccumulator(1, C, P, dev, layers, list(range(nsteps)), True, "sparsemax",
-                                         per_pair=True)
-            else:
-                acc = gen.accumulator(1, C, P, layers, list(range(nsteps)), True, "sparsemax", False)
+            acc = gen.accumulator(1, C, P, layers, list(range(nsteps)), True, "sparsemax", False,
+                                  per_pair=bool(wl.get("per_pair")))
             gen.denoise(inps[i], sched, guidance, acc)
             return acc.finalize()
     else:
@@ -198,6 +205,7 @@ def run_ours(args, rank, world, local_rank):
     # graph cannot be read back.  The graph-replay number is reported beside it.)
     ops.LAUNCHES = 0
     ops.ATTN_EVENTS = []
+    ops.HBM_EVENTS = {}
     clocks = ClockSampler(local_rank)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -214,6 +222,16 @@ def run_ours(args, rank, world, local_rank):
     n_attn = len(ops.ATTN_EVENTS)
     attn_flops = sum(B * attention_flops(Pq, Tq, Cq, Hq, Cq > 0) for _, B, Pq, Tq, Cq, Hq in ops.ATTN_EVENTS)
     ops.ATTN_EVENTS = None
+    pk = peaks()
+    hbm = {}
+    for name, evs in ops.HBM_EVENTS.items():
+        ms_k = sum(ev[0].elapsed_time(ev[1]) for ev, _ in evs)
+        by = sum(nb for _, nb in evs)
+        gbs = by / (ms_k * 1e-3) / 1e9 if ms_k > 0 else 0.0
+        hbm[name] = {"achieved": gbs, "frac": gbs / pk["hbm"], "launches_timed": len(evs),
+                     "avg_launch_us": 1e3 * ms_k / max(len(evs), 1), "algorithmic_MB_per_launch": by / max(len(evs), 1) / 1e6,
+                     "share_of_step": ms_k / ms_dev}
+    ops.HBM_EVENTS = None
     # the same K steps as the product runs them by default (whole forwards replayed as CUDA graphs)
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
@@ -266,13 +284,15 @@ def run_ours(args, rank, world, local_rank):
         t = torch.tensor([ms_dev, ms_e2e, ms_graph], device=dev, dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         ms_dev, ms_e2e, ms_graph = t.tolist()
-    pk = peaks()
     ach = attn_flops / (attn_ms * 1e-3) / 1e12 if attn_ms > 0 else 0.0
-    traffic = None
+    # DRAM bytes per launch of K2 cannot be counted from inside the process: the figure is the one
+    # `ncu --set full` capture of this command committed under profiles/ (file named in the line)
+    traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "k2_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and args.config == "schnell-1024":
         with open(tpath) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
+            tj = json.load(f)
+        traffic, traffic_src = tj.get("dram_bytes_per_launch"), tj.get("source")
     images = args.steps * batch * (1 if sharded else world)
     blocks = "19 double + 38 single blocks" if mode == "generate" else "19 double blocks (stop_after_multimodal_attentions)"
     line = {
@@ -300,25 +320,43 @@ def run_ours(args, rank, world, local_rank):
         "roofline": {"kernel": "ca_joint_attention (K2, tcgen05 one-way joint attention)",
                      "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s",
                      "frac": ach / pk["tflops"], "peak_source": pk["source"], "traffic": traffic,
+                     "traffic_source": traffic_src, "frac_of_burst_peak": ach / pk["tflops_burst"],
                      "launches_timed": n_attn, "avg_launch_ms": attn_ms / max(n_attn, 1),
                      "share_of_step": attn_ms / ms_dev},
+        "roofline_hbm": {"bound": "hbm", "peak": pk["hbm"], "unit": "GB/s", "peak_source": pk["source"],
+                         "note": "every launch of the timed region bracketed by CUDA events on its stream; "
+                                 "algorithmic bytes per SURVEY.md 8d; at this size the operands are partly "
+                                 "L2-resident (the producer kernel just wrote them), so frac can exceed what HBM "
+                                 "alone would allow; the text stream's K1c launches overlap image-stream GEMMs",
+                         "kernels": hbm},
         "graph_replay": {"enabled": graphed, "value": images / (ms_graph * 1e-3), "unit": "images/s",
                          "ms_per_step": ms_graph / args.steps,
                          "note": "same K steps, inputs resident, whole forwards replayed as CUDA graphs "
                                  "(the default of the public API, used by e2e)"},
     }
+    if want_gpu_ref:
+        ours_maps = (np.asarray(out.concept_heatmaps), np.asarray(out.cross_attention_maps))
+        gen.model._graphs.clear()                       # free the captured graphs' private pools
+        torch.cuda.empty_cache()
+        # the last timed e2e step used host_lat[warmup + steps - 1] == dev_lat[-1]
+        gr = run_gpu_reference(wl, sd, gen, dev, dev_lat, prompt, concepts, ours_maps)
+        gr["speedup_e2e_over_gpu_reference"] = line["e2e"]["value"] / gr["value"]
+        gr["speedup_value_over_gpu_reference"] = line["value"] / gr["value"]
+        line["gpu_reference"] = gr
     return line, out
 
 
 def run_reference(args):
-    """CPU arm: the oracle (fp32 port of the reference's PyTorch path, executing the same
-    op sequence incl. the full (C+P)^2 second attention and the stack-then-einsum heatmap
-    step) on all host cores.  One step = a bounded SAMPLE of one image of the workload:
-    1 double block + 1 single block + the heatmap computation of one (timestep, 4 layers)
-    slice at full dimensions, extrapolated linearly:
-        t_image = nsteps * (19 t_double + 38 t_single) + nsteps * t_heat
-    (the reference's model-independent glue — embeddings, final layer — is < 0.1 %)."""
+    """CPU arm: the reference's OWN modules (oracle/_ref: ModifiedDoubleStreamBlock,
+    ModifiedSingleStreamBlock, compute_heatmaps_from_vectors — unmodified files; the oracle port
+    only if oracle/_ref is absent) in fp32 on all host cores, default nn.Module init, synthetic
+    inputs of the workload's shapes.  One step = a bounded SAMPLE of one image of the workload:
+    1 double block (incl. the full (C+P)^2 second attention it executes) + 1 single block + the
+    heatmap computation of one (timestep, 4 layers) slice at full dimensions, extrapolated linearly:
+        t_image = nsteps * (depth t_double + depth_single t_single) + nsteps * t_heat
+    (the model-independent glue — embeddings, final layer — is < 0.1 %)."""
     import oracle
+    from oracle import reference_modules as rm
     from conceptattention_b200.weights import CONFIGS, FluxParams, init_state_dict
     wl = WORKLOADS[args.config]
     pm = CONFIGS[wl["model"]]
@@ -328,27 +366,49 @@ def run_reference(args):
     side, C, nsteps, layers = wl["side"], wl["C"], wl["nsteps"], wl["layers"]
     D, H = pm.hidden_size, pm.num_heads
     P, T = (side // 16) ** 2, {"flux-schnell": 256, "flux-dev": 512}.get(wl["model"], 128)
-    one = FluxParams(**{**pm.asdict(), "depth": 1, "depth_single_blocks": 1})
-    sd = init_state_dict(one, seed=0)
     g = torch.Generator().manual_seed(0)
     img, txt, con = (torch.randn(1, n, D, generator=g) for n in (P, T, C))
     vec, cvec = torch.randn(1, D, generator=g), torch.randn(1, D, generator=g)
     ids = oracle.image_ids(1, side // 16, side // 16)
-    pe = oracle.rope_table(torch.cat((torch.zeros(1, T, 3), ids), 1), pm.axes_dim, pm.theta)
-    pe_c = oracle.rope_table(torch.cat((torch.zeros(1, C, 3), ids), 1), pm.axes_dim, pm.theta)
     nl = min(len(layers), 4)
+    use_ref = rm.available()
+    if use_ref:
+        ns = rm.load()
+        from concept_attention.flux.src.flux.modules.layers import EmbedND
+        torch.manual_seed(0)
+        dbl = ns.ModifiedDoubleStreamBlock(D, H, mlp_ratio=pm.mlp_ratio, qkv_bias=pm.qkv_bias).eval()
+        sgl = ns.ModifiedSingleStreamBlock(D, H, mlp_ratio=pm.mlp_ratio).eval()
+        embed = EmbedND(dim=D // H, theta=pm.theta, axes_dim=pm.axes_dim)
+        pe = embed(torch.cat((torch.zeros(1, T, 3), ids), 1))
+        pe_c = embed(torch.cat((torch.zeros(1, C, 3), ids), 1))
+        kind, what = "reference", f"the reference's own modules ({ns.kind})"
+    else:
+        one = FluxParams(**{**pm.asdict(), "depth": 1, "depth_single_blocks": 1})
+        sd = init_state_dict(one, seed=0)
+        pe = oracle.rope_table(torch.cat((torch.zeros(1, T, 3), ids), 1), pm.axes_dim, pm.theta)
+        pe_c = oracle.rope_table(torch.cat((torch.zeros(1, C, 3), ids), 1), pm.axes_dim, pm.theta)
+        kind, what = "port", "the oracle port (oracle/_ref absent)"
 
     def sample():
         t0 = time.perf_counter()
-        i2, t2, c2, vecs = oracle.double_block(sd, "double_blocks.0", H, img, txt, vec, pe, con, cvec, pe_c)
+        if use_ref:
+            i2, t2, c2, vecs = dbl(img=img, txt=txt, vec=vec, pe=pe, concepts=con, concept_vec=cvec, concept_pe=pe_c)
+        else:
+            i2, t2, c2, vecs = oracle.double_block(sd, "double_blocks.0", H, img, txt, vec, pe, con, cvec, pe_c)
         t1 = time.perf_counter()
-        oracle.single_block(sd, "single_blocks.0", H, torch.cat((t2, i2), 1), vec, pe)
+        if use_ref:
+            sgl(torch.cat((t2, i2), 1), vec=vec, pe=pe)
+        else:
+            oracle.single_block(sd, "single_blocks.0", H, torch.cat((t2, i2), 1), vec, pe)
         t2_ = time.perf_counter()
         for a, b in (("output_space_image_vectors", "output_space_concept_vectors"),
                      ("cross_attention_image_vectors", "cross_attention_concept_vectors")):
             iv = vecs[a][None, None].expand(1, nl, *vecs[a].shape)
             cv = vecs[b][None, None].expand(1, nl, *vecs[b].shape)
-            oracle.heatmaps_from_vectors(iv, cv, list(range(nl)), [0])
+            if use_ref:
+                ns.compute_heatmaps_from_vectors(iv, cv, layer_indices=list(range(nl)), timesteps=[0])
+            else:
+                oracle.heatmaps_from_vectors(iv, cv, list(range(nl)), [0])
         t3 = time.perf_counter()
         if wl["mode"] == "encode":            # one pass through the 19 double blocks + heatmaps
             return pm.depth * (t1 - t0) + (t3 - t2_)
@@ -362,18 +422,124 @@ def run_reference(args):
     est = [sample() for _ in range(steps)]
     t_img = statistics.mean(est)
     val = 1.0 / t_img
-    desc = (f"per step: 1 double block + 1 single block + heatmaps of 1 timestep x {nl} layers x 2 spaces at "
-            f"full size (P={P},T={T},C={C},D={D}) fp32, extrapolated to {nsteps} steps x (19+38) blocks")
+    desc = (f"{what}, fp32, {cores} threads; per step: 1 double block + 1 single block + heatmaps of 1 timestep x "
+            f"{nl} layers x 2 spaces at full size (P={P},T={T},C={C},D={D}), extrapolated linearly to {nsteps} steps x "
+            f"({pm.depth}+{pm.depth_single_blocks}) blocks (not a whole image: a whole image is ~{t_img:.0f} s of CPU time)")
     return {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "images/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": max(args.warmup, 1), "ms_per_step": t_img * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic (random-init weights, randn inputs)",
         "config": {"workload": f"{args.config}: {wl['model']} {side}x{side}, P={P} T={T} C={C}, {nsteps} denoise steps",
-                   "note": "CPU host cores; rank 0 only; bounded sample extrapolated"},
-        "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": "port", "sample": desc},
+                   "note": "CPU host cores; rank 0 only; bounded sample extrapolated (ms_per_step is the "
+                           "extrapolated time of one image, not the wall time of a step)"},
+        "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": kind, "sample": desc,
+                         "sample_wall_s": per_sample},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+
+
+def run_gpu_reference(wl, sd, gen, dev, dev_lat, prompt, concepts, ours_maps, n_images=2):
+    """The real bar: the reference's own PyTorch path in bf16 on the
+    SAME B200, same random-init weights (shared storage), same inputs: its `denoise`
+    (flux/src/flux/sampling.py:96-152: ModifiedFluxDiT with two full SDPA calls per double block,
+    the per-layer / per-step torch.stack's) followed by `compute_heatmaps_from_vectors` for both
+    spaces and the fp32 host copy of the maps (concept_attention_pipeline.py:150-172).  Inputs are
+    resident in HBM, like `value`.  Not timed: T5/CLIP (synthetic in both arms), the VAE, and the
+    reference generator's model.cpu()/.to(device) bounce per image (image_generator.py:183-194),
+    which would only make it slower."""
+    import oracle
+    from oracle import reference_modules as rm
+    from conceptattention_b200 import sampling
+    pm = gen.params
+    side, nsteps, layers = wl["side"], wl["nsteps"], wl["layers"]
+    P = (side // 16) ** 2
+    sched = sampling.get_schedule(nsteps, P, shift=(not gen.is_schnell))
+    guidance = wl.get("guidance", 0.0)
+    if rm.available():
+        ns = rm.load()
+        model = rm.build_dit(pm.asdict(), sd, dev, torch.bfloat16)
+        kind = f"the reference's own modules ({ns.kind}), bf16, cuda"
+
+        def image(lat):
+            inp = gen.prepare_inputs(prompt, concepts, lat)
+            x, _, st = ns.denoise(model, img=inp["img"], img_ids=inp["img_ids"], txt=inp["txt"],
+                                  txt_ids=inp["txt_ids"], vec=inp["vec"], timesteps=sched, guidance=guidance,
+                                  concepts=inp["concepts"], concept_ids=inp["concept_ids"],
+                                  concept_vec=inp["concept_vec"])
+            out, cross = rm.heatmaps(st, layers, range(nsteps))
+            return out.to(torch.float32).cpu().numpy(), cross.to(torch.float32).cpu().numpy()
+    else:
+        sdd = {k: v.to(dev, torch.bfloat16) for k, v in sd.items()}
+        kind = "the oracle port of the reference op sequence (oracle/_ref absent), bf16, cuda"
+
+        def image(lat):
+            inp = gen.prepare_inputs(prompt, concepts, lat)
+            x, st = oracle.denoise(sdd, pm.asdict(), inp["img"], inp["img_ids"].float(), inp["txt"],
+                                   inp["txt_ids"].float(), inp["vec"], sched, guidance=guidance,
+                                   concepts=inp["concepts"], concept_ids=inp["concept_ids"].float(),
+                                   concept_vec=inp["concept_vec"])
+            maps = [oracle.heatmaps_from_vectors(st[a], st[b], layers, range(nsteps)) for a, b in
+                    (("output_space_image_vectors", "output_space_concept_vectors"),
+                     ("cross_attention_image_vectors", "cross_attention_concept_vectors"))]
+            return maps[0].float().cpu().numpy(), maps[1].float().cpu().numpy()
+
+    with torch.no_grad():
+        image(dev_lat[0])                       # warm-up (cuBLAS heuristics, SDPA backend selection, allocator)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n_images):
+            maps = image(dev_lat[-1 - (i % len(dev_lat))])
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n_images
+    # parity of the two arms on the last image (same latents as the last timed step of `value`)
+    par = {}
+    if ours_maps is not None:
+        for tag, got, ref in (("concept_heatmaps", ours_maps[0], maps[0]), ("cross_attention_maps", ours_maps[1], maps[1])):
+            got, ref = np.asarray(got, dtype=np.float32).reshape(ref.shape), np.asarray(ref, dtype=np.float32)
+            par[tag] = {"max_rel": float((np.abs(got - ref) / np.maximum(np.abs(ref), 1e-2)).max()),
+                        "mean_abs": float(np.abs(got - ref).mean()),
+                        "argmax_mask_agreement": float((got.argmax(-3) == ref.argmax(-3)).mean())}
+    return {"value": 1e3 / ms, "unit": "images/s", "ms_per_image": ms, "images_timed": n_images, "kind": kind,
+            "what": "denoise (all DiT blocks, two SDPA calls per double block, vector stacks) + "
+                    "compute_heatmaps_from_vectors x 2 spaces + fp32 host copy; inputs resident in HBM",
+            "parity_vs_ours_same_image": par}
+
+
+def other_configs(args, rank, world, local_rank):
+    """Short runs of the other BASELINE.json configurations in the same process (extra keys of
+    the line; the bench line itself stays configs[1]).  N = 1: configs[2] (encode sweep),
+    configs[3] (flux-dev, 20 concepts, 28 steps, per-(timestep, layer) maps) and configs[4] on one GPU
+    (the strong-scaling base).  N > 1: configs[2] data-parallel and configs[4] with the heads
+    sharded over the N ranks (the curve that has a collective in it)."""
+    import gc
+    out = {}
+    todo = [("encode-512", 3, 3), ("schnell-2048-hs", 2, 3)]
+    if world == 1:
+        todo.insert(1, ("dev-1024-c20", 1, 3))
+    for name, steps, warmup in todo:
+        if name == "schnell-2048-hs" and world > 1 and 24 % world:
+            continue
+        gc.collect()
+        torch.cuda.empty_cache()
+        a = argparse.Namespace(**{**vars(args), "config": name, "steps": steps, "warmup": warmup,
+                                  "hs_mode": "auto"})
+        try:
+            ln, _ = run_ours(a, rank, world, local_rank, secondary=True)
+        except Exception as e:                              # report, do not lose the bench line
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+            continue
+        out[name] = {k: ln[k] for k in ("value", "unit", "ms_per_step", "steps", "scaling", "n_gpus")}
+        out[name].update(workload=ln["config"]["workload"], parallelism=ln["config"]["parallelism"],
+                         images_per_step_per_gpu=ln["config"]["images_per_step_per_gpu"],
+                         e2e=ln["e2e"]["value"], graph_replay=ln["graph_replay"]["value"],
+                         k2_tflops=ln["roofline"]["achieved"], k2_frac=ln["roofline"]["frac"],
+                         k2_avg_launch_ms=ln["roofline"]["avg_launch_ms"],
+                         hbm_kernels={k: round(v["frac"], 3) for k, v in ln["roofline_hbm"]["kernels"].items()},
+                         clocks=ln["clocks"])
+    return out
 
 
 def main():
@@ -392,6 +558,8 @@ def main():
     ap.add_argument("--tp-overlap", action="store_true",
                     help="head-sharded mode: two token chunks on two streams around the all-reduces (A/B)")
     ap.add_argument("--no-side-stream", action="store_true", help="text stream on the main CUDA stream (A/B)")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip the reference-on-the-same-GPU arm")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the short runs of the other configs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -407,6 +575,8 @@ def main():
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     args.warmup = max(args.warmup, 3)
     line, _ = run_ours(args, rank, world, local_rank)
+    if args.config == "schnell-1024" and not args.no_other_configs:
+        line["other_configs"] = other_configs(args, rank, world, local_rank)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             torch.cuda.empty_cache()

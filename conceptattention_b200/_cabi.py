@@ -15,6 +15,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libconcept
 CA_OK = 0
 NORM = {"softmax": 0, "sparsemax": 1, "entmax15": 2, "none": 3}
 ATTN_BOTH, ATTN_CROSS_ONLY, ATTN_SELF_ONLY, ATTN_NEITHER = 0, 1, 2, 3
+MAX_CONCEPTS = 32            # CA_MAX_CONCEPTS
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 
@@ -31,6 +32,9 @@ SIGNATURES = {
     "ca_joint_attention_workspace_bytes": [_i] * 6,
     "ca_joint_attention_ws": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, C.c_size_t, _p],
     "ca_heatmap_accumulate": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p],
+    "ca_heatmap_accumulate_pair": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p,
+                                   _i64, _p, _i, _p],
+    "ca_norm_accumulate_pair": [_p, _i, _i, _i, _i, _i, _p, _p, _p],
     "ca_heatmap_logits": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _p, _p],
     "ca_norm_accumulate": [_p, _i, _i, _i, _i, _i, _p, _p],
     "ca_concept_linear_normalize": [_p, _p, _i, _i64, _p],

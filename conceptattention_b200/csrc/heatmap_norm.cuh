@@ -71,7 +71,17 @@ struct HmArgs {
   const __nv_bfloat16* con; int64_t csb, css, csc;
   int nseg, seg_len, B, P, C, norm, round_bf16;
   float* acc;      // fused: acc += norm(logits);   logits-only: acc = logits
+  // optional per-(timestep, layer) slot: pair[slot][b,c,p] = norm(logits) in the same pass
+  // (concept_attention_pipeline.py:76-77 before the mean).  slot = *pair_slot (a DEVICE int,
+  // so a captured forward can be replayed for every timestep) + pair_slot_off.
+  float* pair = nullptr; int64_t pair_stride = 0; const int* pair_slot = nullptr; int pair_slot_off = 0;
 };
+
+__device__ __forceinline__ float* pair_base(const HmArgs& a) {
+  if (!a.pair) return nullptr;
+  const int slot = (a.pair_slot ? __ldg(a.pair_slot) : 0) + a.pair_slot_off;
+  return a.pair + (int64_t)slot * a.pair_stride;
+}
 
 
 // tcgen05/TMA variant (k3_heatmap_tc.cu).  Returns CA_ERR_UNSUPPORTED when the shape does not

@@ -88,6 +88,11 @@ heatmap_kernel(const HmArgs a) {
         for (int c = 0; c < CT; ++c) old[c] = c < a.C ? __ldcg(dst + (int64_t)c * a.P) : 0.f;
 #pragma unroll
         for (int c = 0; c < CT; ++c) if (c < a.C) dst[(int64_t)c * a.P] = old[c] + sum[r][c];
+        if (float* pb = pair_base(a)) {
+          float* pd = pb + (int64_t)b * a.C * a.P + p;
+#pragma unroll
+          for (int c = 0; c < CT; ++c) if (c < a.C) pd[(int64_t)c * a.P] = sum[r][c];
+        }
       }
     }
   }
@@ -96,7 +101,8 @@ heatmap_kernel(const HmArgs a) {
 // K4 alone: one thread per (b,p).
 template <int CT>
 __global__ void norm_accumulate_kernel(const float* __restrict__ logits, float* __restrict__ acc,
-                                       int B, int P, int C, int norm, int round_bf16) {
+                                       int B, int P, int C, int norm, int round_bf16,
+                                       float* __restrict__ pair) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)B * P) return;
   const int b = (int)(i / P), p = (int)(i - (int64_t)b * P);
@@ -109,6 +115,10 @@ __global__ void norm_accumulate_kernel(const float* __restrict__ logits, float* 
   normalise<CT>(z, C, norm, round_bf16 != 0);
 #pragma unroll
   for (int c = 0; c < CT; ++c) if (c < C) acc[((int64_t)b * C + c) * P + p] = old[c] + z[c];
+  if (pair) {
+#pragma unroll
+    for (int c = 0; c < CT; ++c) if (c < C) pair[((int64_t)b * C + c) * P + p] = z[c];
+  }
 }
 
 // Column-wise min-shift / sum normalisation of a [C,K] bf16 matrix (utils.py:35-44).
@@ -173,6 +183,19 @@ extern "C" ca_status ca_heatmap_accumulate(const void* img, int64_t isb, int64_t
   return ca::launch_heatmap<false>(a, (cudaStream_t)stream);
 }
 
+extern "C" ca_status ca_heatmap_accumulate_pair(const void* img, int64_t isb, int64_t iss, int64_t isp,
+                                                const void* con, int64_t csb, int64_t css, int64_t csc,
+                                                int nseg, int seg_len, int B, int P, int C, int norm,
+                                                int round_bf16, float* acc, float* pair,
+                                                int64_t pair_stride, const int* pair_slot,
+                                                int pair_slot_off, void* stream) {
+  ca::HmArgs a{(const __nv_bfloat16*)img, isb, iss, isp, (const __nv_bfloat16*)con, csb, css, csc,
+               nseg, seg_len, B, P, C, norm, round_bf16, acc};
+  a.pair = pair; a.pair_stride = pair_stride; a.pair_slot = pair_slot; a.pair_slot_off = pair_slot_off;
+  if (pair && pair_stride < (int64_t)B * C * P) return CA_ERR_INVALID_ARG;
+  return ca::launch_heatmap<false>(a, (cudaStream_t)stream);
+}
+
 extern "C" ca_status ca_heatmap_logits(const void* img, int64_t isb, int64_t iss, int64_t isp,
                                        const void* con, int64_t csb, int64_t css, int64_t csc,
                                        int nseg, int seg_len, int B, int P, int C, float* logits,
@@ -182,8 +205,8 @@ extern "C" ca_status ca_heatmap_logits(const void* img, int64_t isb, int64_t iss
   return ca::launch_heatmap<true>(a, (cudaStream_t)stream);
 }
 
-extern "C" ca_status ca_norm_accumulate(const float* logits, int B, int P, int C, int norm,
-                                        int round_bf16, float* acc, void* stream) {
+extern "C" ca_status ca_norm_accumulate_pair(const float* logits, int B, int P, int C, int norm,
+                                             int round_bf16, float* acc, float* pair, void* stream) {
   if (!logits || !acc || B < 0 || P < 0 || C <= 0) return CA_ERR_INVALID_ARG;
   if (C > CA_MAX_CONCEPTS) return CA_ERR_UNSUPPORTED;
   if (norm < CA_NORM_SOFTMAX || norm > CA_NORM_NONE) return CA_ERR_INVALID_ARG;
@@ -191,12 +214,17 @@ extern "C" ca_status ca_norm_accumulate(const float* logits, int B, int P, int C
   if (n == 0) return CA_OK;
   const unsigned blocks = (unsigned)((n + 255) / 256);
   auto st = (cudaStream_t)stream;
-  if (C <= 4) ca::norm_accumulate_kernel<4><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16);
-  else if (C <= 8) ca::norm_accumulate_kernel<8><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16);
-  else if (C <= 16) ca::norm_accumulate_kernel<16><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16);
-  else ca::norm_accumulate_kernel<32><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16);
+  if (C <= 4) ca::norm_accumulate_kernel<4><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16, pair);
+  else if (C <= 8) ca::norm_accumulate_kernel<8><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16, pair);
+  else if (C <= 16) ca::norm_accumulate_kernel<16><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16, pair);
+  else ca::norm_accumulate_kernel<32><<<blocks, 256, 0, st>>>(logits, acc, B, P, C, norm, round_bf16, pair);
   CA_LAUNCH_CHECK();
   return CA_OK;
+}
+
+extern "C" ca_status ca_norm_accumulate(const float* logits, int B, int P, int C, int norm,
+                                        int round_bf16, float* acc, void* stream) {
+  return ca_norm_accumulate_pair(logits, B, P, C, norm, round_bf16, acc, nullptr, stream);
 }
 
 extern "C" ca_status ca_concept_linear_normalize(const void* con, void* out, int C, int64_t K,

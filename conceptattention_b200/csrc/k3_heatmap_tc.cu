@@ -41,6 +41,7 @@ struct SmemTc {
 struct HmTcParams {
   int B, P, C, seg_len, chunks_per_cta, norm, round_bf16;
   float* acc;
+  float* pair; int64_t pair_stride; const int* pair_slot; int pair_slot_off;   // see HmArgs
 };
 
 template <int NPAD, int CT, bool kLogitsOnly>
@@ -149,6 +150,12 @@ heatmap_tc_kernel(const __grid_constant__ CUtensorMap tma, const __grid_constant
         for (int c = 0; c < CT; ++c) old[c] = c < p.C ? __ldcg(dst + (int64_t)c * p.P) : 0.f;
 #pragma unroll
         for (int c = 0; c < CT; ++c) if (c < p.C) dst[(int64_t)c * p.P] = old[c] + zz[c];
+        if (p.pair) {
+          const int slot = (p.pair_slot ? __ldg(p.pair_slot) : 0) + p.pair_slot_off;
+          float* pd = p.pair + (int64_t)slot * p.pair_stride + (int64_t)b * p.C * p.P + pi;
+#pragma unroll
+          for (int c = 0; c < CT; ++c) if (c < p.C) pd[(int64_t)c * p.P] = zz[c];
+        }
       }
     }
   }
@@ -210,7 +217,8 @@ ca_status launch_heatmap_tc(const HmArgs& a, bool logits_only, cudaStream_t st) 
   while (S < smax && (int64_t)tiles * a.B * S < 128 && chunks % (2 * S) == 0 && chunks / (2 * S) >= 2)
     S *= 2;
   if (g_heatmap_split > 0 && g_heatmap_split <= smax && chunks % g_heatmap_split == 0) S = g_heatmap_split;
-  HmTcParams p{a.B, a.P, a.C, a.seg_len, chunks / S, a.norm, a.round_bf16, a.acc};
+  HmTcParams p{a.B, a.P, a.C, a.seg_len, chunks / S, a.norm, a.round_bf16, a.acc,
+               a.pair, a.pair_stride, a.pair_slot, a.pair_slot_off};
 #define CA_TC(NP, CT)                                                                 \
   (logits_only ? launch_tc<NP, CT, true>(tma, tmb, p, tiles, S, st)                   \
                : launch_tc<NP, CT, false>(tma, tmb, p, tiles, S, st))

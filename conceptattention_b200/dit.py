@@ -57,7 +57,14 @@ class HeatmapAccumulator:
     """
 
     def __init__(self, B, C, P, device, layer_indices, timesteps=None, softmax=True,
-                 attention_norm="sparsemax", round_bf16=False, per_pair=False, buffer=None):
+                 attention_norm="sparsemax", round_bf16=False, per_pair=False, buffer=None,
+                 pair_buffer=None):
+        """`per_pair=True` (BASELINE config 4) also keeps every selected pair's normalised map —
+        the reference's `heatmaps[timesteps][:, layer_indices]` before the mean
+        (concept_attention_pipeline.py:76-77) — in ONE fp32 buffer
+        [Nt_sel, L_sel, 2, B, C, P] (unique sorted timesteps x layers; spaces output, cross),
+        written by the same kernel launch that updates the running sum.  The slot of the current
+        timestep lives in a device int, so a captured forward serves every timestep."""
         if not (softmax or attention_norm in ("softmax", "entmax15", "sparsemax")):
             raise ValueError(f"Unknown attention_norm={attention_norm}")
         self.norm = "softmax" if (softmax or attention_norm == "softmax") else attention_norm
@@ -72,35 +79,54 @@ class HeatmapAccumulator:
             self.acc = buffer.zero_()
         self.count = 0
         self.step = 0
-        self.per_pair = {} if per_pair else None      # (t, l) -> [2,B,C,P]
+        self.pairs = None
+        if per_pair:
+            self.pair_steps = sorted(set(self.timesteps)) if self.timesteps is not None else [0]
+            self.pair_layers = sorted(set(self.layers))
+            shape = (len(self.pair_steps), len(self.pair_layers), 2, B, C, P)
+            if pair_buffer is None:
+                self.pairs = torch.zeros(shape, device=device, dtype=torch.float32)
+            else:
+                assert tuple(pair_buffer.shape) == shape and pair_buffer.dtype == torch.float32
+                self.pairs = pair_buffer.zero_()
+            self.pair_slot = torch.zeros(1, device=device, dtype=torch.int32)
+
+    @property
+    def per_pair(self):
+        return self.pairs
 
     def begin_step(self, step_index: int):
         self.step = step_index
+        if self.pairs is not None and step_index in self.pair_steps:
+            # first slot of this timestep; read by the kernels at run time (graph-replay safe)
+            self.pair_slot.fill_(self.pair_steps.index(step_index) * len(self.pair_layers) * 2)
 
     def multiplicity(self, layer: int) -> int:
         mt = 1 if self.timesteps is None else self.timesteps.count(self.step)
         return mt * self.layers.count(layer)
 
+    def _pair_args(self, layer, space):
+        if self.pairs is None:
+            return {}
+        return dict(pair=self.pairs.view(-1, self.B, self.C, self.P), pair_slot=self.pair_slot,
+                    pair_slot_off=self.pair_layers.index(layer) * 2 + space)
+
     def add(self, layer, attn_img, attn_con, q_pre, P, T):
         """attn_img [B,P,D]; attn_con [B,C,D] view; q_pre [B,H,P+T+C,128]."""
         m = self.multiplicity(layer)
-        if m == 0:
-            return
-        targets = [self.acc] * m
-        if self.per_pair is not None:
-            slot = torch.zeros_like(self.acc)
-            self.per_pair[(self.step, layer)] = slot
-            targets.append(slot)
-        for acc in targets:
-            ops.heatmap_accumulate(attn_img, attn_con, acc[0], self.norm, self.round_bf16)
-            ops.heatmap_accumulate(q_pre[:, :, :P], q_pre[:, :, P + T:], acc[1], self.norm,
-                                   self.round_bf16, per_head=True)
+        for rep in range(m):
+            kw = (lambda s: self._pair_args(layer, s)) if rep == 0 else (lambda s: {})
+            ops.heatmap_accumulate(attn_img, attn_con, self.acc[0], self.norm, self.round_bf16, **kw(0))
+            ops.heatmap_accumulate(q_pre[:, :, :P], q_pre[:, :, P + T:], self.acc[1], self.norm,
+                                   self.round_bf16, per_head=True, **kw(1))
         self.count += m
 
     def signature(self, depth):
         """What a captured forward bakes in for this accumulator at the current step."""
         return (self.acc.data_ptr(), self.norm, self.round_bf16,
-                tuple(self.multiplicity(i) for i in range(depth)))
+                tuple(self.multiplicity(i) for i in range(depth)),
+                None if self.pairs is None else (self.pairs.data_ptr(), self.pair_slot.data_ptr(),
+                                                 tuple(self.pair_layers)))
 
     def note_replay(self, depth):
         """Host bookkeeping of one replayed forward (the kernels ran inside the graph)."""
@@ -110,17 +136,23 @@ class HeatmapAccumulator:
         """Head-sharded form: `logits` fp32 [2,B,C,P] (output space, cross space) are the
         all-reduced sums of the ranks' partial logits; normalise + accumulate (K4)."""
         m = self.multiplicity(layer)
-        if m == 0:
-            return
-        targets = [self.acc] * m
-        if self.per_pair is not None:
-            slot = torch.zeros_like(self.acc)
-            self.per_pair[(self.step, layer)] = slot
-            targets.append(slot)
-        for acc in targets:
+        for rep in range(m):
             for s in range(2):
-                ops.norm_accumulate(logits[s], acc[s], self.norm, self.round_bf16)
+                pair = None
+                if rep == 0 and self.pairs is not None:       # slot chosen on the host here
+                    pair = self.pairs[self.pair_steps.index(self.step), self.pair_layers.index(layer), s]
+                ops.norm_accumulate(logits[s], self.acc[s], self.norm, self.round_bf16, pair=pair)
         self.count += m
+
+    def per_pair_heatmaps(self):
+        """-> (concept [Nt_sel,L_sel,B,C,h,w], cross [...]) fp32 views of the per-pair buffer,
+        axes ordered as `pair_steps` x `pair_layers`."""
+        if self.pairs is None:
+            raise ValueError("accumulator was built without per_pair=True")
+        side = math.isqrt(self.P)
+        shp = self.pairs.shape[:2] + ((self.B, self.C, side, side) if side * side == self.P
+                                      else (self.B, self.C, self.P))
+        return self.pairs[:, :, 0].reshape(shp), self.pairs[:, :, 1].reshape(shp)
 
     def finalize(self):
         """-> (concept_heatmaps, cross_attention_maps), each [B,C,h,w] fp32."""
@@ -279,6 +311,9 @@ class FluxDiTEngine:
         if self._rope_cache.get("key") != key:
             # new id tensors: look the table up by CONTENT (one small D2H per new id set) so
             # equal ids always map to the same table address (captured graphs bake it in)
+            for full, name in ((img_ids, "img_ids"), (txt_ids, "txt_ids"), (concept_ids, "concept_ids")):
+                if full.shape[0] > 1 and not bool((full == full[:1]).all()):
+                    raise ValueError(f"{name} differ across the batch: one RoPE table serves the whole batch")
             ids = torch.cat([t.to(self.device, torch.float32) for t in parts], 0)
             digest = hashlib.sha1(ids.cpu().numpy().tobytes()).hexdigest() + str(tuple(ids.shape))
             tables = self._rope_cache.setdefault("tables", {})
@@ -322,8 +357,9 @@ class FluxDiTEngine:
                     joint_attention_kwargs=joint_attention_kwargs, accumulator=accumulator,
                     collect_vectors=collect_vectors)
         eligible = (self.use_graphs and not collect_vectors and (self.hs is None or self.hs.graph_safe())
-                    and ops.ATTN_EVENTS is None
-                    and (accumulator is None or accumulator.per_pair is None)
+                    and ops.ATTN_EVENTS is None and ops.HBM_EVENTS is None
+                    and (accumulator is None or accumulator.per_pair is None or self.hs is None
+                         or self.hs.world == 1)
                     and concept_vec is not None and img.ndim == 3 and txt.ndim == 3
                     and not torch.cuda.is_current_stream_capturing())
         if not eligible:
@@ -346,7 +382,11 @@ class FluxDiTEngine:
             if self._graph_seen[key] < 2:
                 return self._forward(**args, **rest)
             if len(self._graphs) >= self.max_graphs:          # drop the oldest capture
+                self._graph_seen.pop(next(iter(self._graphs)), None)
                 self._graphs.pop(next(iter(self._graphs)))
+            if len(self._graph_seen) > 4 * self.max_graphs:   # signatures seen once and never again
+                for k in [k for k in self._graph_seen if k not in self._graphs][:2 * self.max_graphs]:
+                    del self._graph_seen[k]
             ent = self._capture(args, rest, rope)
             self._graphs[key] = ent
         elif accumulator is not None:
@@ -356,7 +396,9 @@ class FluxDiTEngine:
                 ent["static"][k].copy_(v, non_blocking=True)
         ent["graph"].replay()
         ops.LAUNCHES += ent["n_launch"]
-        return ent["pred"], {}
+        # a fresh tensor per call, like the launch-by-launch path (the graph's own output buffer is
+        # overwritten by the next replay of this signature)
+        return (ent["pred"].clone() if ent["pred"] is not None else None), {}
 
     def _capture(self, args, rest, rope):
         """Capture one forward on static copies of the per-call tensors.  The accumulator's
@@ -373,7 +415,7 @@ class FluxDiTEngine:
         acc = rest["accumulator"]
         local = self._rope_cache.get("locals", {}).get((rope.data_ptr(), args["img"].shape[1], args["txt"].shape[1]))
         return {"graph": graph, "static": static, "pred": pred, "n_launch": ops.LAUNCHES - n0,
-                "keep": (rope, local, None if acc is None else acc.acc)}
+                "keep": (rope, local, None if acc is None else (acc.acc, acc.pairs, getattr(acc, "pair_slot", None)))}
 
     @torch.no_grad()
     def _forward(self, img, img_ids, txt, txt_ids, concepts, concept_ids, concept_vec, timesteps, y,

@@ -19,10 +19,31 @@ def check(status, what, n_launch=1):
 
 BF16 = torch.bfloat16
 
-# Instrumentation used by bench.py: number of C-ABI kernel launches, and (when
-# ATTN_EVENTS is a list) a CUDA-event pair around every K2 launch on its stream.
+# Instrumentation used by bench.py: number of C-ABI kernel launches, (when ATTN_EVENTS is a
+# list) a CUDA-event pair around every K2 launch on its stream, and (when HBM_EVENTS is a dict)
+# the same around every K1a / K1b / K1c / K3+K4 launch together with its ALGORITHMIC bytes
+# (SURVEY.md section 8d): {kernel: [(event pair, bytes), ...]}.
 LAUNCHES = 0
 ATTN_EVENTS = None
+HBM_EVENTS = None
+
+
+class _timed:
+    """with _timed("K1b", nbytes): launch  — no-op unless bench.py asked for HBM_EVENTS."""
+
+    def __init__(self, name, nbytes):
+        self.name, self.nbytes = name, nbytes
+
+    def __enter__(self):
+        if HBM_EVENTS is not None:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record()
+
+    def __exit__(self, *exc):
+        if HBM_EVENTS is not None and exc[0] is None:
+            self.ev[1].record()
+            HBM_EVENTS.setdefault(self.name, []).append((self.ev, self.nbytes))
+        return False
 
 
 def _stream(t: torch.Tensor) -> int:
@@ -59,10 +80,11 @@ def ln_modulate(x, mod0, mod1=None, split=None, shift_off=0, scale_off=None, out
     if out is None:
         out = torch.empty_like(x)
     scale_off = D if scale_off is None else scale_off
-    check(_cabi.load().ca_ln_modulate(
-        x.data_ptr(), out.data_ptr(), B, N, D, mod0.data_ptr(),
-        mod1.data_ptr() if mod1 is not None else None, N if split is None else split,
-        mod0.stride(0), shift_off, scale_off, _stream(x)), "ca_ln_modulate")
+    with _timed("K1a ln_modulate", 4 * B * N * D):
+        check(_cabi.load().ca_ln_modulate(
+            x.data_ptr(), out.data_ptr(), B, N, D, mod0.data_ptr(),
+            mod1.data_ptr() if mod1 is not None else None, N if split is None else split,
+            mod0.stride(0), shift_off, scale_off, _stream(x)), "ca_ln_modulate")
     return out
 
 
@@ -79,11 +101,12 @@ def gate_residual_ln_modulate(x, y, mod0, mod1=None, split=None, gate_off=0, shi
     assert y.stride(0) == N * y.stride(1) or B == 1
     if want_out and out is None:
         out = torch.empty_like(x)
-    check(_cabi.load().ca_gate_residual_ln_modulate(
-        x.data_ptr(), y.data_ptr(), y.stride(1), out.data_ptr() if want_out else None, B, N, D,
-        mod0.data_ptr(), mod1.data_ptr() if mod1 is not None else None,
-        N if split is None else split, mod0.stride(0), gate_off, shift_off, scale_off,
-        _stream(x)), "ca_gate_residual_ln_modulate")
+    with _timed("K1c gate_residual_ln_modulate", (8 if want_out else 6) * B * N * D):
+        check(_cabi.load().ca_gate_residual_ln_modulate(
+            x.data_ptr(), y.data_ptr(), y.stride(1), out.data_ptr() if want_out else None, B, N, D,
+            mod0.data_ptr(), mod1.data_ptr() if mod1 is not None else None,
+            N if split is None else split, mod0.stride(0), gate_off, shift_off, scale_off,
+            _stream(x)), "ca_gate_residual_ln_modulate")
     return out if want_out else None
 
 
@@ -104,15 +127,17 @@ def qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope, H, want_q_pre=False):
     q, k, v = (torch.empty(B, H, Na + Nb, 128, device=dev, dtype=BF16) for _ in range(3))
     q_pre = torch.empty_like(q) if want_q_pre else None
     sb = scales_b if scales_b is not None else (None, None)
-    check(_cabi.load().ca_qkv_prep(
-        qkv_a.data_ptr(), qkv_a.stride(1), Na,
-        qkv_b.data_ptr() if qkv_b is not None else None,
-        qkv_b.stride(1) if qkv_b is not None else 0, Nb,
-        scales_a[0].data_ptr(), scales_a[1].data_ptr(),
-        sb[0].data_ptr() if sb[0] is not None else None,
-        sb[1].data_ptr() if sb[1] is not None else None,
-        rope.data_ptr(), B, H, q.data_ptr(), k.data_ptr(), v.data_ptr(),
-        q_pre.data_ptr() if want_q_pre else None, _stream(qkv_a)), "ca_qkv_prep")
+    Ntok = B * (Na + Nb)
+    with _timed("K1b qkv_prep", Ntok * (2 * 3 * H * 128 * 2 + 512 + (2 * H * 128 if want_q_pre else 0))):
+        check(_cabi.load().ca_qkv_prep(
+            qkv_a.data_ptr(), qkv_a.stride(1), Na,
+            qkv_b.data_ptr() if qkv_b is not None else None,
+            qkv_b.stride(1) if qkv_b is not None else 0, Nb,
+            scales_a[0].data_ptr(), scales_a[1].data_ptr(),
+            sb[0].data_ptr() if sb[0] is not None else None,
+            sb[1].data_ptr() if sb[1] is not None else None,
+            rope.data_ptr(), B, H, q.data_ptr(), k.data_ptr(), v.data_ptr(),
+            q_pre.data_ptr() if want_q_pre else None, _stream(qkv_a)), "ca_qkv_prep")
     return (q, k, v, q_pre) if want_q_pre else (q, k, v)
 
 
@@ -234,16 +259,36 @@ def _hm_strides(img, con, per_head):
     return B, P, C, 1, K, (img.stride(0), 0, img.stride(1)), (con.stride(0), 0, con.stride(1))
 
 
-def heatmap_accumulate(img, con, acc, norm="softmax", round_bf16=False, per_head=False):
+def heatmap_accumulate(img, con, acc, norm="softmax", round_bf16=False, per_head=False,
+                       pair=None, pair_slot=None, pair_slot_off=0):
     """acc[b,c,p] += norm_c(<img[b,p,:], con[b,c,:]>).  Views with arbitrary
-    batch/row strides are accepted (no copies)."""
+    batch/row strides are accepted (no copies).
+    `pair` (fp32 [S,B,C,P] slots, optional): the same pass also stores this pair's normalised
+    map into slot `pair_slot[0] + pair_slot_off` (`pair_slot`: device int32 tensor or None)."""
     assert img.dtype == BF16 and con.dtype == BF16 and img.is_cuda
     B, P, C, nseg, seg_len, si, sc = _hm_strides(img, con, per_head)
     _req(acc, torch.float32, "acc")
     assert acc.shape == (B, C, P)
-    check(_cabi.load().ca_heatmap_accumulate(
-        img.data_ptr(), si[0], si[1], si[2], con.data_ptr(), sc[0], sc[1], sc[2], nseg, seg_len,
-        B, P, C, NORM[norm], int(round_bf16), acc.data_ptr(), _stream(img)), "ca_heatmap_accumulate")
+    K = nseg * seg_len
+    tm = _timed("K3+K4 heatmap_accumulate", B * (2 * P * K + 2 * C * K + (8 if pair is None else 12) * C * P))
+    if pair is None:
+        with tm:
+            check(_cabi.load().ca_heatmap_accumulate(
+                img.data_ptr(), si[0], si[1], si[2], con.data_ptr(), sc[0], sc[1], sc[2], nseg, seg_len,
+                B, P, C, NORM[norm], int(round_bf16), acc.data_ptr(), _stream(img)), "ca_heatmap_accumulate")
+        return acc
+    _req(pair, torch.float32, "pair")
+    assert pair.ndim == 4 and pair.shape[1:] == (B, C, P)
+    if pair_slot is not None:
+        assert pair_slot.is_cuda and pair_slot.dtype == torch.int32 and pair_slot.numel() == 1
+    else:
+        assert 0 <= pair_slot_off < pair.shape[0]
+    with tm:
+        check(_cabi.load().ca_heatmap_accumulate_pair(
+            img.data_ptr(), si[0], si[1], si[2], con.data_ptr(), sc[0], sc[1], sc[2], nseg, seg_len,
+            B, P, C, NORM[norm], int(round_bf16), acc.data_ptr(), pair.data_ptr(), pair.stride(0),
+            pair_slot.data_ptr() if pair_slot is not None else None, pair_slot_off, _stream(img)),
+            "ca_heatmap_accumulate_pair")
     return acc
 
 
@@ -258,11 +303,16 @@ def heatmap_logits(img, con, per_head=False, out=None):
     return out
 
 
-def norm_accumulate(logits, acc, norm="softmax", round_bf16=False):
+def norm_accumulate(logits, acc, norm="softmax", round_bf16=False, pair=None):
+    """acc += norm_c(logits); `pair` (fp32 [B,C,P], optional) also receives norm_c(logits)."""
     _req(logits, torch.float32, "logits"); _req(acc, torch.float32, "acc")
     B, C, P = logits.shape
-    check(_cabi.load().ca_norm_accumulate(logits.data_ptr(), B, P, C, NORM[norm], int(round_bf16),
-                                          acc.data_ptr(), _stream(logits)), "ca_norm_accumulate")
+    if pair is not None:
+        _req(pair, torch.float32, "pair")
+        assert pair.shape == (B, C, P)
+    check(_cabi.load().ca_norm_accumulate_pair(
+        logits.data_ptr(), B, P, C, NORM[norm], int(round_bf16), acc.data_ptr(),
+        pair.data_ptr() if pair is not None else None, _stream(logits)), "ca_norm_accumulate_pair")
     return acc
 
 

@@ -34,6 +34,10 @@ class ConceptAttentionPipelineOutput:
     image: "PIL.Image.Image | np.ndarray"
     concept_heatmaps: "list[PIL.Image.Image] | np.ndarray"
     cross_attention_maps: "list[PIL.Image.Image] | np.ndarray"
+    # extension (return_per_pair=True): fp32 device tensors [Nt_sel, L_sel, B, C, h, w] — every
+    # selected (timestep, layer) pair's map before the mean (concept_attention_pipeline.py:76-77)
+    per_pair_concept_heatmaps: "torch.Tensor | None" = None
+    per_pair_cross_attention_maps: "torch.Tensor | None" = None
 
 
 def compute_heatmaps_from_vectors(image_vectors, concept_vectors, layer_indices,
@@ -87,27 +91,48 @@ class FluxGenerator:
         self.clip = clip or sampling.SyntheticEmbedder(self.params.vec_in_dim, None, self.device)
         self.ae = ae
         self._acc_buffers = {}
+        self._id_cache = {}
 
-    def accumulator(self, B, C, P, layer_indices, timesteps, softmax, attention_norm, round_bf16):
-        """HeatmapAccumulator on a generator-owned state buffer: the same address call after
-        call, so the engine's captured forwards stay valid from image to image."""
-        buf = self._acc_buffers.get((B, C, P))
-        if buf is None:
-            if len(self._acc_buffers) >= 4:
-                self._acc_buffers.pop(next(iter(self._acc_buffers)))
-            buf = self._acc_buffers[(B, C, P)] = torch.empty(2, B, C, P, device=self.device,
-                                                              dtype=torch.float32)
+    def accumulator(self, B, C, P, layer_indices, timesteps, softmax, attention_norm, round_bf16,
+                    per_pair=False):
+        """HeatmapAccumulator on generator-owned state buffers: the same addresses call after
+        call, so the engine's captured forwards stay valid from image to image.  `per_pair`
+        adds the [Nt_sel, L_sel, 2, B, C, P] fp32 per-(timestep, layer) buffer (config 4:
+        28 x 19 x 2 x 20 x 4096 x 4 B = 349 MB, where the reference stacks 26.8 GB of vectors,
+        flux/src/flux/sampling.py:146-150)."""
+        def owned(key, shape):
+            buf = self._acc_buffers.get(key)
+            if buf is None:
+                if len(self._acc_buffers) >= 6:
+                    self._acc_buffers.pop(next(iter(self._acc_buffers)))
+                buf = self._acc_buffers[key] = torch.empty(shape, device=self.device, dtype=torch.float32)
+            return buf
+        pairs = None
+        if per_pair:
+            nt = len(set(int(t) for t in timesteps)) if timesteps is not None else 1
+            nl = len(set(int(l) for l in layer_indices))
+            pairs = owned(("pairs", nt, nl, B, C, P), (nt, nl, 2, B, C, P))
         return HeatmapAccumulator(B, C, P, self.device, layer_indices, timesteps, softmax,
-                                  attention_norm, round_bf16, buffer=buf)
+                                  attention_norm, round_bf16, per_pair=per_pair,
+                                  buffer=owned((B, C, P), (2, B, C, P)), pair_buffer=pairs)
 
     @torch.inference_mode()
     def prepare_inputs(self, prompt, concepts, latents):
         inp = sampling.prepare(self.t5, self.clip, latents, prompt)
         emb, ids, vec = sampling.embed_concepts(self.clip, self.t5, concepts)
         B = inp["img"].shape[0]
-        inp["concepts"] = emb.to(self.device).expand(B, -1, -1)
+        inp["concepts"] = emb.to(self.device, non_blocking=True).expand(B, -1, -1)
         inp["concept_ids"] = ids.to(self.device).expand(B, -1, -1)
-        inp["concept_vec"] = vec.to(self.device).expand(B, -1)
+        inp["concept_vec"] = vec.to(self.device, non_blocking=True).expand(B, -1)
+        # position ids depend on the shapes only (sampling.py:40-47, utils.py:25): keep ONE set
+        # per shape so the engine's RoPE-table cache hits by tensor identity (no D2H, no hash)
+        key = tuple(tuple(inp[k].shape) for k in ("img_ids", "txt_ids", "concept_ids"))
+        ids = self._id_cache.get(key)
+        if ids is None:
+            if len(self._id_cache) >= 8:
+                self._id_cache.pop(next(iter(self._id_cache)))
+            ids = self._id_cache[key] = tuple(inp[k].contiguous() for k in ("img_ids", "txt_ids", "concept_ids"))
+        inp["img_ids"], inp["txt_ids"], inp["concept_ids"] = ids
         return inp
 
     @torch.inference_mode()
@@ -154,6 +179,14 @@ def _colour(maps: np.ndarray, cmap: str):
     return out
 
 
+def _check_concepts(concepts):
+    """The kernels hold one concept per register slot (CA_MAX_CONCEPTS = 32); the reference
+    accepts any count.  Reject early with a clear message instead of a kernel status deep inside."""
+    if not 1 <= len(concepts) <= _cabi.MAX_CONCEPTS:
+        raise ValueError(f"between 1 and {_cabi.MAX_CONCEPTS} concepts are supported per call, got "
+                         f"{len(concepts)}; split the concept list over several calls")
+
+
 class ConceptAttentionFluxPipeline:
     """Generate images with Flux, or 'encode' existing ones, and return per-concept
     heatmaps.  Same constructor and methods as the reference class
@@ -177,12 +210,13 @@ class ConceptAttentionFluxPipeline:
                        guidance: float = 0.0, timesteps=None, softmax: bool = True,
                        attention_norm: str = "sparsemax", cmap="plasma",
                        joint_attention_kwargs=None, latents=None, round_bf16=False,
-                       decode_image=True) -> ConceptAttentionPipelineOutput:
+                       decode_image=True, return_per_pair=False) -> ConceptAttentionPipelineOutput:
         gen = self.flux_generator
         depth = gen.params.depth
         assert return_cross_attention is False, "Not supported yet"
         assert all(0 <= i < depth for i in layer_indices), "Invalid layer index"
         assert height == width, "Height and width must be the same for now"
+        _check_concepts(concepts)
         if timesteps is None:
             timesteps = list(range(num_inference_steps))
         dev = gen.device
@@ -194,9 +228,11 @@ class ConceptAttentionFluxPipeline:
         sched = sampling.get_schedule(num_inference_steps, inp["img"].shape[1],
                                       shift=(not gen.is_schnell))
         B, P, C = inp["img"].shape[0], inp["img"].shape[1], len(concepts)
-        acc = gen.accumulator(B, C, P, layer_indices, timesteps, softmax, attention_norm, round_bf16)
+        acc = gen.accumulator(B, C, P, layer_indices, timesteps, softmax, attention_norm, round_bf16,
+                              per_pair=return_per_pair)
         x = gen.denoise(inp, sched, guidance, acc, joint_attention_kwargs)
         concept_heatmaps, cross_attention_maps = acc.finalize()
+        pp = acc.per_pair_heatmaps() if return_per_pair else (None, None)
         image = gen.decode(x, height, width) if decode_image else None
         # one D2H of [2,C,h,w] fp32 (the reference moves both maps separately, :171-172)
         both = torch.stack((concept_heatmaps[0], cross_attention_maps[0])).cpu().numpy()
@@ -205,7 +241,9 @@ class ConceptAttentionFluxPipeline:
             concept_heatmaps = _colour(concept_heatmaps, cmap)
             cross_attention_maps = _colour(cross_attention_maps, cmap)
         return ConceptAttentionPipelineOutput(image=image, concept_heatmaps=concept_heatmaps,
-                                              cross_attention_maps=cross_attention_maps)
+                                              cross_attention_maps=cross_attention_maps,
+                                              per_pair_concept_heatmaps=pp[0],
+                                              per_pair_cross_attention_maps=pp[1])
 
     # ------------------------------------------------------------------------------
     @torch.no_grad()
@@ -226,6 +264,7 @@ class ConceptAttentionFluxPipeline:
         depth = gen.params.depth
         assert all(0 <= i < depth for i in layer_indices), "Invalid layer index"
         assert height == width, "Height and width must be the same for now"
+        _check_concepts(concepts)
         dev = gen.device
         if isinstance(image, torch.Tensor):
             clean = image.to(dev, torch.bfloat16, non_blocking=True)

@@ -19,8 +19,12 @@ class SyntheticEmbedder:
     """Callable like HFEmbedder: list[str] | str -> [n, max_length, dim] (T5-like)
     or [n, dim] (CLIP-like, pooled).  Values are randn seeded by crc32(prompt)."""
 
-    def __init__(self, dim: int, max_length: int | None, device="cpu", dtype=torch.bfloat16):
+    def __init__(self, dim: int, max_length: int | None, device="cpu", dtype=torch.bfloat16, pin=False):
+        """`pin=True` (host embedder feeding a GPU): per-prompt embeddings and the stacked result
+        live in pinned host memory, so the `.to(cuda, non_blocking=True)` that follows is a real
+        asynchronous H2D copy instead of a staged pageable one."""
         self.dim, self.max_length, self.device, self.dtype = dim, max_length, device, dtype
+        self.pin = pin and torch.cuda.is_available()
         self._cache = {}
 
     def to(self, device):
@@ -38,8 +42,14 @@ class SyntheticEmbedder:
             if t not in self._cache:
                 g = torch.Generator().manual_seed(zlib.crc32(t.encode("utf-8")))
                 shape = (self.dim,) if self.max_length is None else (self.max_length, self.dim)
-                self._cache[t] = torch.randn(shape, generator=g).to(self.dtype)
+                e = torch.randn(shape, generator=g).to(self.dtype)
+                self._cache[t] = e.pin_memory() if self.pin else e
             outs.append(self._cache[t])
+        if len(outs) == 1:
+            return outs[0][None].to(self.device)            # a view: stays pinned
+        if self.pin:
+            out = torch.empty((len(outs),) + tuple(outs[0].shape), dtype=self.dtype, pin_memory=True)
+            return torch.stack(outs, out=out).to(self.device)
         return torch.stack(outs).to(self.device)
 
 
@@ -86,13 +96,18 @@ def prepare(t5, clip, img, prompt):
     if vec.shape[0] == 1 and bs > 1:
         vec = vec.repeat(bs, 1)
     dev = img.device
-    return {"img": x, "img_ids": image_ids(bs, h // 2, w // 2, dev), "txt": txt.to(dev),
-            "txt_ids": torch.zeros(bs, txt.shape[1], 3, device=dev), "vec": vec.to(dev)}
+    return {"img": x, "img_ids": image_ids(bs, h // 2, w // 2, dev), "txt": txt.to(dev, non_blocking=True),
+            "txt_ids": torch.zeros(bs, txt.shape[1], 3, device=dev), "vec": vec.to(dev, non_blocking=True)}
 
 
 def embed_concepts(clip, t5, concepts, batch_size=1):
     """First T5 token per concept, zero ids, zeroed CLIP vector (utils.py:6-33)."""
-    emb = torch.stack([t5(c)[0, 0, :] for c in concepts]).unsqueeze(0)
+    toks = [t5(c)[0, 0, :] for c in concepts]
+    if toks[0].device.type == "cpu" and getattr(t5, "pin", False):
+        emb = torch.stack(toks, out=torch.empty((len(toks),) + tuple(toks[0].shape), dtype=toks[0].dtype,
+                                                pin_memory=True)).unsqueeze(0)
+    else:
+        emb = torch.stack(toks).unsqueeze(0)
     ids = torch.zeros(batch_size, emb.shape[1], 3)
     vec = torch.zeros_like(clip(" ".join(concepts)))
     return emb, ids, vec

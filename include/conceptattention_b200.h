@@ -149,6 +149,22 @@ ca_status ca_heatmap_accumulate(const void* img, int64_t img_stride_b, int64_t i
                                 int nseg, int seg_len, int B, int P, int C,
                                 int norm, int round_bf16, float* acc, void* stream);
 
+/* Same pass, additionally keeping THIS (timestep, layer) pair's normalised map: the
+ * reference's heatmaps[t][:, l] before the mean (concept_attention_pipeline.py:76-77;
+ * experiments/per_layer_segmentation), BASELINE config 4's per-layer / per-timestep mode.
+ *   pair[slot][b,c,p] = norm_c(logits[b,:,p]),  slot = (*pair_slot_dev or 0) + pair_slot_off,
+ * slots `pair_stride` floats apart (>= B*C*P).  pair_slot_dev is a DEVICE int read by the
+ * kernel, so one captured CUDA graph of a forward serves every timestep; pair == NULL is
+ * ca_heatmap_accumulate. */
+ca_status ca_heatmap_accumulate_pair(const void* img, int64_t img_stride_b, int64_t img_stride_s,
+                                     int64_t img_stride_p,
+                                     const void* con, int64_t con_stride_b, int64_t con_stride_s,
+                                     int64_t con_stride_c,
+                                     int nseg, int seg_len, int B, int P, int C,
+                                     int norm, int round_bf16, float* acc, float* pair,
+                                     int64_t pair_stride, const int* pair_slot_dev,
+                                     int pair_slot_off, void* stream);
+
 /* K3 only: partial logits of a head/feature slice, written (not accumulated) as
  * fp32 [B,C,P] — the buffer a head-sharded run all-reduces before K4. */
 ca_status ca_heatmap_logits(const void* img, int64_t img_stride_b, int64_t img_stride_s,
@@ -161,6 +177,10 @@ ca_status ca_heatmap_logits(const void* img, int64_t img_stride_b, int64_t img_s
 /* K4 only: acc += norm_c(logits) on fp32 [B,C,P]. */
 ca_status ca_norm_accumulate(const float* logits, int B, int P, int C, int norm,
                              int round_bf16, float* acc, void* stream);
+
+/* K4 with the per-pair output of ca_heatmap_accumulate_pair (pair fp32 [B,C,P], nullable). */
+ca_status ca_norm_accumulate_pair(const float* logits, int B, int P, int C, int norm,
+                                  int round_bf16, float* acc, float* pair, void* stream);
 
 /* utils.py:35-44 applied over the concept axis of a [C,K] bf16 matrix
  * (normalize_concepts=True, concept_attention_pipeline.py:53-54). */

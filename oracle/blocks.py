@@ -161,9 +161,9 @@ def denoise(sd, params, img, img_ids, txt, txt_ids, vec, timesteps, guidance=4.0
     """Euler sampler that stacks every step's vectors (sampling.py:96-152).
     Returns (img, {key: [Nt,L,B,...]})."""
     collected = {k: [] for k in VECTOR_KEYS}
-    g = torch.full((img.shape[0],), guidance, dtype=img.dtype)
+    g = torch.full((img.shape[0],), guidance, dtype=img.dtype, device=img.device)
     for t_curr, t_prev in zip(timesteps[:-1], timesteps[1:]):
-        t_vec = torch.full((img.shape[0],), t_curr, dtype=img.dtype)
+        t_vec = torch.full((img.shape[0],), t_curr, dtype=img.dtype, device=img.device)
         pred, vecs = dit_forward(sd, params, img, img_ids, txt, txt_ids, concepts, concept_ids,
                                  concept_vec, t_vec, vec, g,
                                  joint_attention_kwargs=joint_attention_kwargs)

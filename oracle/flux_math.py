@@ -34,7 +34,7 @@ def rope_table(ids: torch.Tensor, axes_dim, theta: int) -> torch.Tensor:
     mats = []
     for a, dim in enumerate(axes_dim):
         assert dim % 2 == 0
-        expo = torch.arange(0, dim, 2, dtype=torch.float64) / dim
+        expo = torch.arange(0, dim, 2, dtype=torch.float64, device=ids.device) / dim
         omega = 1.0 / (float(theta) ** expo)
         ang = ids[..., a].to(torch.float64)[..., None] * omega      # [B,N,dim/2]
         c, s = torch.cos(ang), torch.sin(ang)
@@ -80,7 +80,7 @@ def timestep_embedding(t, dim, max_period=10000, time_factor=1000.0):
     """Sinusoidal embedding (layers.py:28-49), cos first then sin."""
     t = time_factor * t
     half = dim // 2
-    freqs = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32) / half)
+    freqs = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32, device=t.device) / half)
     args = t[:, None].float() * freqs[None]
     emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
     if dim % 2:

@@ -24,8 +24,69 @@ SHAPES = [  # name, B, H, P, T, C
 ]
 
 
+def bench_sdpa(name, B, H, P, T, C, iters, pk):
+    """The op K2 replaces, as the reference runs it on this GPU: two
+    F.scaled_dot_product_attention calls per double block (modified_double_stream_block.py:112-116
+    over [txt;img] and :162-166 over [concept;img], whose image rows are then discarded), one per
+    single block (flux/src/flux/math.py:6-12).  bf16, no mask, torch's default backend choice plus
+    each backend forced.  `TFLOPs_executed` counts what the library kernel computes,
+    `TFLOPs_algorithmic` credits only K2's FLOP count (what the path needs) over the time of BOTH calls."""
+    import torch.nn.functional as F
+    from torch.nn.attention import SDPBackend, sdpa_kernel
+    N1, N2 = T + P, C + P
+    mk = lambda n: [[torch.randn(B, H, n, 128, device="cuda").to(torch.bfloat16) for _ in range(3)] for _ in range(2)]
+    a1, a2 = mk(N1), (mk(N2) if C > 0 else None)
+    need = 4 * 128 * H * B * (N1 ** 2 + C * (C + P))
+
+    def timed(fn):
+        for i in range(3):
+            fn(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    backends = [("default", None), ("flash", SDPBackend.FLASH_ATTENTION), ("cudnn", SDPBackend.CUDNN_ATTENTION),
+                ("efficient", SDPBackend.EFFICIENT_ATTENTION)]
+    for bname, be in backends:
+        try:
+            ctx = (lambda: sdpa_kernel([be])) if be is not None else None
+            def run1(i):
+                return F.scaled_dot_product_attention(*a1[i % 2])
+            def run2(i):
+                return F.scaled_dot_product_attention(*a2[i % 2])
+            if ctx is not None:
+                with ctx():
+                    ms1 = timed(run1)
+                    ms2 = timed(run2) if C > 0 else 0.0
+            else:
+                ms1 = timed(run1)
+                ms2 = timed(run2) if C > 0 else 0.0
+        except Exception as e:                                  # backend not available for this shape
+            print(json.dumps({"kernel": "F.scaled_dot_product_attention", "backend": bname, "shape": name,
+                              "error": f"{type(e).__name__}: {e}"[:160]}), flush=True)
+            continue
+        tf1 = 4 * 128 * H * B * N1 ** 2 / ms1 / 1e9
+        tf2 = 4 * 128 * H * B * N2 ** 2 / ms2 / 1e9 if C > 0 else None
+        alg = need / (ms1 + ms2) / 1e9
+        print(json.dumps({"kernel": "F.scaled_dot_product_attention", "backend": bname, "shape": name, "B": B,
+                          "H": H, "P": P, "T": T, "C": C, "ms_txt_img": round(ms1, 4),
+                          "ms_concept_img": round(ms2, 4), "ms_both": round(ms1 + ms2, 4),
+                          "TFLOPs_executed_txt_img": round(tf1, 1),
+                          "TFLOPs_executed_concept_img": None if tf2 is None else round(tf2, 1),
+                          "TFLOPs_algorithmic": round(alg, 1),
+                          "frac_sustained_peak_txt_img": round(tf1 / pk["bf16_tflops_sustained"], 3),
+                          "frac_sustained_peak_algorithmic": round(alg / pk["bf16_tflops_sustained"], 3)}),
+              flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--sdpa", action="store_true", help="also time the reference's SDPA calls on the same shapes")
     ap.add_argument("--impls", default="0,2,3")
     ap.add_argument("--only", default="")
     ap.add_argument("--iters", type=int, default=20)
@@ -62,6 +123,9 @@ def main():
         lib.ca_debug_set_attention_impl(0)
         del sets
         torch.cuda.empty_cache()
+        if args.sdpa:
+            bench_sdpa(name, B, H, P, T, C, args.iters, pk)
+            torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":

@@ -1,5 +1,5 @@
-"""bench.py contract on CPU: the reference arm (oracle port timed on the host cores) prints the
-agreed JSON line, and our arm has no CPU fallback (it must fail, not quietly time something else)."""
+"""bench.py contract on CPU: the reference arm (the reference's own modules from oracle/_ref, or the
+oracle port when they are absent, timed on the host cores) prints the agreed JSON line, and our arm has no CPU fallback (it must fail, not quietly time something else)."""
 import json
 import os
 import subprocess
@@ -23,7 +23,9 @@ def test_reference_arm_prints_the_contract_line():
     assert line["metric"].startswith("concept-heatmap images/sec") and line["value"] > 0
     assert line["n_gpus"] == 1 and line["steps"] == 1 and line["warmup"] == 1 and line["vs_baseline"] is None
     cb = line["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["sample"] and cb["value"] == line["value"]
+    from oracle import reference_modules as rm
+    assert cb["kind"] == ("reference" if rm.available() else "port")
+    assert cb["cores"] >= 1 and cb["sample"] and cb["value"] == line["value"]
     assert line["e2e"] == {"value": line["value"], "unit": "images/s", "h2d_bytes_per_step": 0,
                            "d2h_bytes_per_step": 0}
     assert "tiny-256" in line["config"]["workload"] and "model" not in line["config"]
