@@ -1320,6 +1320,522 @@ attn_persist_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
+// =============================================================================
+// v5: thread-per-row softmax, one warpgroup per query tile, single pass over S.
+// Same CTA shape and TMEM map as v1 (two 128-row query tiles, 384 threads, S0 S1 O0 O1), but
+//  * a softmax thread owns one whole query row: the 128 S values are pulled out of TMEM with four
+//    tcgen05.ld in flight and ONE wait (v1/v2 made two passes with nine serialised loads, v3 splits a
+//    row over two threads and pays a 256-thread barrier per tile), the row max is a FMNMX3 tree over
+//    registers, exp2 runs in place and P is packed over the consumed S registers;
+//  * P is handed to the tensor core in two halves (keys [0,64) and [64,128), one mbarrier each), so
+//    the first four PV MMAs of a tile run while the softmax thread is still on the second half;
+//  * the two warpgroups work on DIFFERENT tiles and drift half a period apart (S0 and S1 complete
+//    1024 tensor cycles apart), so on every SM sub-partition one warp's TMEM load / max / TMEM store
+//    phases sit under the other warp's MUFU stream.
+// Why (measured, profiles/r02_k2_vs_sdpa.md): the library attention torch picks on this GPU runs
+// the (T+P)^2 part at 1386 TFLOP/s where v3 reaches 1140 — v3's period per key step is twice its
+// per-tile softmax time (the tiles alternate on the same 256 threads), here it is one softmax
+// latency plus one QK+PV.
+// =============================================================================
+struct SmemV5 {
+  uint8_t q[2][kTileBytes];
+  uint8_t kv[kKvStages][kTileBytes];
+  uint64_t q_full[2], kv_full[kKvStages], kv_empty[kKvStages], s_full[2], p_full[2][2], o_done;
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void v5_producer(SmemV5& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
+                                            const CUtensorMap* tmv, const UnitV1& u, int bh) {
+  int item = 0;
+  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
+    mbar_expect_tx(bar, kTileBytes);
+    tma_load_3d(dst, tm, bar, 0, row0, bh);
+    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+  };
+  auto load_kv = [&](const CUtensorMap* tm, int j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+    const int slot = item % kKvStages;
+    mbar_wait(&sm.kv_empty[slot], ((item / kKvStages) & 1) ^ 1);
+    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    ++item;
+  };
+  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
+  load_kv(tmk, 0);
+  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
+  load_kv(tmv, 0);
+  for (int j = 1; j < u.n_local; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
+}
+
+__device__ __forceinline__ void v5_mma(SmemV5& sm, uint32_t tmem, const UnitV1& u) {
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  // Descriptors differ from tile to tile only in the 14-bit start-address field (bytes >> 4), so the
+  // issue loop is one 32-bit add per operand: base descriptor of buffer 0 + slot * (tile bytes >> 4)
+  // + the k-step offset (a compile-time constant once the loops are unrolled).
+  const uint64_t dq = make_smem_desc(smem_u32(sm.q[0]), 16, 1024);
+  const uint64_t dk = make_smem_desc(smem_u32(sm.kv[0]), 16, 1024);             // K tile: K-major
+  const uint64_t dv = make_smem_desc(smem_u32(sm.kv[0]), kHalfBytes, 1024);     // V tile: MN-major
+  auto kv_wait = [&](int item) {
+    const int slot = item % kKvStages;
+    mbar_wait(&sm.kv_full[slot], (item / kKvStages) & 1);
+    return slot;
+  };
+  auto qk = [&](int t, int kslot) {                      // S_t = Q_t K^T
+    const uint64_t qa = dq + (uint64_t)(t * (kTileBytes >> 4)), ka = dk + (uint64_t)(kslot * (kTileBytes >> 4));
+#pragma unroll
+    for (int kk = 0; kk < kD / 16; ++kk) {
+      const uint32_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+      mma_ss(tmem + t * 128, qa + off, ka + off, idesc_qk, kk > 0);
+    }
+    mma_commit(&sm.s_full[t]);
+  };
+  auto pv = [&](int t, int vslot, int j) {               // O_t (+)= P_t V in two key halves
+    const uint64_t va = dv + (uint64_t)(vslot * (kTileBytes >> 4));
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      mbar_wait(&sm.p_full[t][hf], j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 4 * hf; kk < 4 * hf + 4; ++kk)
+        mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kk * 8, va + (uint64_t)(kk * (2048 >> 4)), idesc_pv,
+               j > 0 || kk > 0);
+    }
+  };
+  const bool two = u.n_q == 2;
+  mbar_wait(&sm.q_full[0], 0);
+  int ks = kv_wait(0);
+  tc_fence_after();
+  qk(0, ks);
+  if (two) { mbar_wait(&sm.q_full[1], 0); tc_fence_after(); qk(1, ks); }
+  mma_commit(&sm.kv_empty[ks]);
+  for (int j = 0; j < u.n_local; ++j) {
+    const bool has_next = j + 1 < u.n_local;
+    const int vs = kv_wait(2 * j + 1);
+    if (has_next) ks = kv_wait(2 * j + 2);
+    tc_fence_after();
+    pv(0, vs, j);
+    if (has_next) qk(0, ks);
+    if (two) pv(1, vs, j);
+    mma_commit(&sm.kv_empty[vs]);
+    if (has_next) {
+      if (two) qk(1, ks);
+      mma_commit(&sm.kv_empty[ks]);
+    }
+  }
+  mma_commit(&sm.o_done);
+}
+
+template <int kPolyEvery>
+__device__ __forceinline__ void v5_softmax(SmemV5& sm, uint32_t tmem, const UnitV1& u,
+                                           const AttnParams& p, int t, int b, int h) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
+  const float scale = p.scale_log2;
+  const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+  float m_used = -INFINITY, l_sum = 0.f;
+
+#pragma unroll 1
+  for (int j = 0; j < u.n_local; ++j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+    mbar_wait(&sm.s_full[t], j & 1);
+    tc_fence_after();
+    uint32_t s[kBN];
+    tmem_ld32(t_s, s);
+    tmem_ld32(t_s + 32, s + 32);
+    tmem_ld32(t_s + 64, s + 64);
+    tmem_ld32(t_s + 96, s + 96);
+    tmem_wait_ld32(s);
+    tmem_wait_ld32(s + 32);
+    tmem_wait_ld32(s + 64);
+    tmem_wait_ld32(s + 96);
+    if (valid < kBN) {                                      // ragged last tile of a key segment
+#pragma unroll
+      for (int i = 0; i < kBN; ++i) if (i >= valid) s[i] = 0xff800000u;   // -inf
+    }
+    // row max: four independent FMNMX3 chains
+    float mc[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) mc[c] = __uint_as_float(s[c]);
+#pragma unroll
+    for (int i = 4; i < kBN; i += 8) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        mc[c] = fmaxf(fmaxf(mc[c], __uint_as_float(s[i + c])), __uint_as_float(s[(i + 4 + c) & (kBN - 1)]));
+    }
+    const float mx = fmaxf(fmaxf(mc[0], mc[1]), fmaxf(mc[2], mc[3]));
+    const bool grow = (mx - m_used) * scale > kRescaleThreshold;   // true on the first tile
+    const float m_new = grow ? mx : m_used;
+    if (j > 0 && __any_sync(0xffffffffu, grow)) {
+      // PV_t(j-1) has completed: the commit behind s_full[t] covers it.  Rare (lazy threshold).
+      const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
+      l_sum *= alpha;
+#pragma unroll 1
+      for (int c = 0; c < kD; c += 8) {
+        uint32_t rc[8];
+        tmem_ld8(t_o + c, rc);
+        tmem_wait_ld8(rc);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+        tmem_st8(t_o + c, rc);
+      }
+      tmem_wait_st();
+    }
+    m_used = m_new;
+    const float mb = m_used * scale;
+    const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
+    uint64_t rsa = pk64(0.f, 0.f), rsb = pk64(0.f, 0.f);
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int e = 64 * hf + 2 * i;
+        const uint64_t x2 = fma2(pk64(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), scale2, nmb2);
+        float e0, e1;
+        if (use_poly<kPolyEvery>(i)) {
+          exp2_poly2(x2, e0, e1);
+        } else {
+          float x0, x1;
+          upk64(x2, x0, x1);
+          e0 = ex2(x0); e1 = ex2(x1);
+        }
+        if (i & 1) rsb = add2(rsb, pk64(e0, e1)); else rsa = add2(rsa, pk64(e0, e1));
+        pk[i] = pack2(e0, e1);
+      }
+      tmem_st32(t_s + hf * 32, pk);                       // P_t keys [64 hf, 64 hf + 64) over S_t columns
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.p_full[t][hf]);
+    }
+    {
+      float r0, r1, r2, r3;
+      upk64(rsa, r0, r1); upk64(rsb, r2, r3);
+      l_sum += (r0 + r1) + (r2 + r3);
+    }
+  }
+
+  // ---- epilogue: O_t / l -> bf16 "B L (H D)" ---------------------------------------
+  mbar_wait(&sm.o_done, 0);
+  tc_fence_after();
+  const float inv_l = 1.f / l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + c, r);
+    tmem_wait_ld32(r);
+    if (row < q_rows) {
+      float o[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+      store_out_row(p, b, h, q_row0 + row, o, inv_l, c, 32);
+    }
+  }
+}
+
+template <int kPolyEvery>
+__global__ void __launch_bounds__(384, 1)
+attn_v5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+               const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV5& sm = *reinterpret_cast<SmemV5*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const UnitV1 u = decode_unit(p, blockIdx.x);
+  if (u.n_local == 0) return;
+  const int bh = u.bh, b = bh / p.H, h = bh - b * p.H;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
+    for (int i = 0; i < kKvStages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm.s_full[i], 1);
+      mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
+    }
+    mbar_init(&sm.o_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp < 4) {
+    // register pool of a 384-thread CTA: 384 x 168 = 64512 = 128 x 88 + 256 x 208
+    setmaxnreg_dec<88>();
+    if (warp == 0) {
+      if (elect_one()) v5_producer(sm, &tmq, &tmk, &tmv, u, bh);
+    } else if (warp == 1) {
+      if (elect_one()) v5_mma(sm, tmem, u);
+    }
+  } else {
+    setmaxnreg_inc<208>();
+    const int t = (warp >> 2) - 1;
+    if (t < u.n_q) v5_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+// =============================================================================
+// v6: v5 with S double-buffered per query tile.  The 128 TMEM columns of S_t hold TWO 64-key
+// score buffers; a key tile is processed as two chunks c = 2j + h:
+//     S_t[h] = Q_t K[64h:64h+64]^T   (8 x tcgen05.mma N = 64)
+//     O_t   += P_t[h] V[64h:64h+64]  (4 x tcgen05.mma, P over the first 32 columns of S_t[h])
+// and the MMA warp runs ONE chunk ahead of the softmax:  QK(c+2) is issued right behind PV(c), so
+// while a softmax thread works on chunk c the scores of chunk c+1 are already in TMEM (v5: the
+// warpgroup idles through PV + QK of its own tile, 36 % of its samples on the s_full wait).  Both
+// warpgroups stay busy, the tensor pipe always has a queued chunk of the other buffer.
+// The one ordering this breaks: s_full of chunk c no longer implies that PV(c-1) has completed,
+// so the (rare, lazy) rescale of O waits on pv_done[t], committed behind every PV.
+// =============================================================================
+struct SmemV6 {
+  uint8_t q[2][kTileBytes];
+  uint8_t kv[kKvStages][kTileBytes];
+  uint64_t q_full[2], kv_full[kKvStages], kv_empty[kKvStages], s_full[2][2], p_full[2][2], pv_done[2], o_done;
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void v6_mma(SmemV6& sm, uint32_t tmem, const UnitV1& u) {
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, 64, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  const uint64_t dq = make_smem_desc(smem_u32(sm.q[0]), 16, 1024);
+  const uint64_t dk = make_smem_desc(smem_u32(sm.kv[0]), 16, 1024);             // K tile: K-major
+  const uint64_t dv = make_smem_desc(smem_u32(sm.kv[0]), kHalfBytes, 1024);     // V tile: MN-major
+  auto kv_wait = [&](int item) {
+    const int slot = item % kKvStages;
+    mbar_wait(&sm.kv_full[slot], (item / kKvStages) & 1);
+    return slot;
+  };
+  auto qk = [&](int t, int kslot, int hf) {              // S_t[hf] = Q_t K[64 hf : 64 hf + 64]^T
+    const uint64_t qa = dq + (uint64_t)(t * (kTileBytes >> 4));
+    const uint64_t ka = dk + (uint64_t)(kslot * (kTileBytes >> 4) + hf * ((64 * 128) >> 4));
+#pragma unroll
+    for (int kk = 0; kk < kD / 16; ++kk) {
+      const uint32_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+      mma_ss(tmem + t * 128 + hf * 64, qa + off, ka + off, idesc_qk, kk > 0);
+    }
+    mma_commit(&sm.s_full[t][hf]);
+  };
+  auto pv = [&](int t, int vslot, int j, int hf) {       // O_t (+)= P_t[hf] V[64 hf : 64 hf + 64]
+    const uint64_t va = dv + (uint64_t)(vslot * (kTileBytes >> 4) + hf * ((4 * 2048) >> 4));
+    mbar_wait(&sm.p_full[t][hf], j & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk)
+      mma_ts(tmem + 256 + t * 128, tmem + t * 128 + hf * 64 + kk * 8, va + (uint64_t)(kk * (2048 >> 4)), idesc_pv,
+             j > 0 || hf > 0 || kk > 0);
+    mma_commit(&sm.pv_done[t]);
+  };
+  const bool two = u.n_q == 2;
+  mbar_wait(&sm.q_full[0], 0);
+  int ks = kv_wait(0);
+  tc_fence_after();
+  qk(0, ks, 0);
+  if (two) { mbar_wait(&sm.q_full[1], 0); tc_fence_after(); qk(1, ks, 0); }
+  qk(0, ks, 1);
+  if (two) qk(1, ks, 1);
+  mma_commit(&sm.kv_empty[ks]);
+  for (int j = 0; j < u.n_local; ++j) {
+    const bool has_next = j + 1 < u.n_local;
+    const int vs = kv_wait(2 * j + 1);
+    if (has_next) ks = kv_wait(2 * j + 2);
+    tc_fence_after();
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      pv(0, vs, j, hf);
+      if (has_next) qk(0, ks, hf);
+      if (two) {
+        pv(1, vs, j, hf);
+        if (has_next) qk(1, ks, hf);
+      }
+    }
+    mma_commit(&sm.kv_empty[vs]);
+    if (has_next) mma_commit(&sm.kv_empty[ks]);
+  }
+  mma_commit(&sm.o_done);
+}
+
+__device__ __forceinline__ void v6_producer(SmemV6& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
+                                            const CUtensorMap* tmv, const UnitV1& u, int bh) {
+  int item = 0;
+  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
+    mbar_expect_tx(bar, kTileBytes);
+    tma_load_3d(dst, tm, bar, 0, row0, bh);
+    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+  };
+  auto load_kv = [&](const CUtensorMap* tm, int j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+    const int slot = item % kKvStages;
+    mbar_wait(&sm.kv_empty[slot], ((item / kKvStages) & 1) ^ 1);
+    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    ++item;
+  };
+  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
+  load_kv(tmk, 0);
+  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
+  load_kv(tmv, 0);
+  for (int j = 1; j < u.n_local; ++j) { load_kv(tmk, j); load_kv(tmv, j); }
+}
+
+template <int kPolyEvery>
+__device__ __forceinline__ void v6_softmax(SmemV6& sm, uint32_t tmem, const UnitV1& u,
+                                           const AttnParams& p, int t, int b, int h) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
+  const float scale = p.scale_log2;
+  const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+  float m_used = -INFINITY, l_sum = 0.f;
+  const uint64_t scale2 = pk64(scale, scale);
+
+#pragma unroll 1
+  for (int j = 0; j < u.n_local; ++j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      mbar_wait(&sm.s_full[t][hf], j & 1);
+      tc_fence_after();
+      uint32_t s[64];
+      tmem_ld32(t_s + hf * 64, s);
+      tmem_ld32(t_s + hf * 64 + 32, s + 32);
+      tmem_wait_ld32(s);
+      tmem_wait_ld32(s + 32);
+      if (valid < kBN) {                                    // ragged last tile of a key segment
+#pragma unroll
+        for (int i = 0; i < 64; ++i) if (hf * 64 + i >= valid) s[i] = 0xff800000u;   // -inf
+      }
+      float mc[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) mc[c] = __uint_as_float(s[c]);
+#pragma unroll
+      for (int i = 4; i < 64; i += 8) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          mc[c] = fmaxf(fmaxf(mc[c], __uint_as_float(s[i + c])), __uint_as_float(s[(i + 4 + c) & 63]));
+      }
+      const float mx = fmaxf(fmaxf(mc[0], mc[1]), fmaxf(mc[2], mc[3]));
+      // a chunk that lies wholly past the segment end (valid <= 64, hf = 1) has mx = -inf: nothing grows
+      const bool grow = (mx - m_used) * scale > kRescaleThreshold;   // true on the first chunk
+      const float m_new = grow ? mx : m_used;
+      const int c_idx = 2 * j + hf;
+      if (c_idx > 0 && __any_sync(0xffffffffu, grow)) {
+        // rare (lazy threshold): O must hold every PV up to chunk c-1 before it is rescaled
+        mbar_wait(&sm.pv_done[t], (c_idx - 1) & 1);
+        tc_fence_after();
+        const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
+        l_sum *= alpha;
+#pragma unroll 1
+        for (int c = 0; c < kD; c += 8) {
+          uint32_t rc[8];
+          tmem_ld8(t_o + c, rc);
+          tmem_wait_ld8(rc);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+          tmem_st8(t_o + c, rc);
+        }
+        tmem_wait_st();
+      }
+      m_used = m_new;
+      const float mb = m_used * scale;
+      const uint64_t nmb2 = pk64(-mb, -mb);
+      uint64_t rsa = pk64(0.f, 0.f), rsb = pk64(0.f, 0.f);
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const uint64_t x2 = fma2(pk64(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), scale2, nmb2);
+        float e0, e1;
+        if (use_poly<kPolyEvery>(i)) {
+          exp2_poly2(x2, e0, e1);
+        } else {
+          float x0, x1;
+          upk64(x2, x0, x1);
+          e0 = ex2(x0); e1 = ex2(x1);
+        }
+        if (i & 1) rsb = add2(rsb, pk64(e0, e1)); else rsa = add2(rsa, pk64(e0, e1));
+        pk[i] = pack2(e0, e1);
+      }
+      tmem_st32(t_s + hf * 64, pk);                       // P_t[hf] over the first 32 columns of S_t[hf]
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.p_full[t][hf]);
+      float r0, r1, r2, r3;
+      upk64(rsa, r0, r1); upk64(rsb, r2, r3);
+      l_sum += (r0 + r1) + (r2 + r3);
+    }
+  }
+
+  // ---- epilogue: O_t / l -> bf16 "B L (H D)" ---------------------------------------
+  mbar_wait(&sm.o_done, 0);
+  tc_fence_after();
+  const float inv_l = 1.f / l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + c, r);
+    tmem_wait_ld32(r);
+    if (row < q_rows) {
+      float o[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+      store_out_row(p, b, h, q_row0 + row, o, inv_l, c, 32);
+    }
+  }
+}
+
+template <int kPolyEvery>
+__global__ void __launch_bounds__(384, 1)
+attn_v6_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+               const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV6& sm = *reinterpret_cast<SmemV6*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const UnitV1 u = decode_unit(p, blockIdx.x);
+  if (u.n_local == 0) return;
+  const int bh = u.bh, b = bh / p.H, h = bh - b * p.H;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
+    for (int i = 0; i < kKvStages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm.s_full[i][0], 1); mbar_init(&sm.s_full[i][1], 1);
+      mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
+      mbar_init(&sm.pv_done[i], 1);
+    }
+    mbar_init(&sm.o_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp < 4) {
+    // register pool of a 384-thread CTA: 384 x 168 = 64512 >= 128 x 96 + 256 x 200
+    setmaxnreg_dec<96>();
+    if (warp == 0) {
+      if (elect_one()) v6_producer(sm, &tmq, &tmk, &tmv, u, bh);
+    } else if (warp == 1) {
+      if (elect_one()) v6_mma(sm, tmem, u);
+    }
+  } else {
+    setmaxnreg_inc<200>();
+    const int t = (warp >> 2) - 1;
+    if (t < u.n_q) v6_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
 // CA_ATTN_NEITHER: concept_attn = concept_v  (modified_double_stream_block.py:157-159),
 // i.e. a head-merge copy of the concept rows of V.
 __global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnParams p) {
@@ -1504,7 +2020,24 @@ extern "C" ca_status ca_joint_attention_ws(const void* q, const void* k, const v
     }
     const int64_t ctas = (int64_t)p.n_dp + 2 * p.sk_sms + p.n_concept;
     if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
-    if (ctas > 0 && g_attention_impl == 14) {
+    if (ctas > 0 && g_attention_impl >= 30 && g_attention_impl <= 32 && pl.sk_sms == 0) {
+      // v6 (thread-per-row softmax, S double-buffered in 64-key chunks): 30 = every 4th pair on the
+      // polynomial, 31 = all MUFU, 32 = every 2nd
+      const int smem = (int)sizeof(SmemV6) + 1024;
+      auto kern = g_attention_impl == 31 ? attn_v6_kernel<0> : g_attention_impl == 32 ? attn_v6_kernel<2>
+                                                             : attn_v6_kernel<4>;
+      CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      kern<<<(unsigned)ctas, 384, smem, st>>>(tmq, tmk, tmv, p);
+      CA_LAUNCH_CHECK();
+    } else if (ctas > 0 && g_attention_impl >= 20 && g_attention_impl <= 22 && pl.sk_sms == 0) {
+      // v5 (thread-per-row softmax): 20 = every 4th pair on the polynomial, 21 = all MUFU, 22 = every 2nd
+      const int smem = (int)sizeof(SmemV5) + 1024;
+      auto kern = g_attention_impl == 21 ? attn_v5_kernel<0> : g_attention_impl == 22 ? attn_v5_kernel<2>
+                                                             : attn_v5_kernel<4>;
+      CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      kern<<<(unsigned)ctas, 384, smem, st>>>(tmq, tmk, tmv, p);
+      CA_LAUNCH_CHECK();
+    } else if (ctas > 0 && g_attention_impl == 14) {
       // experimental persistent v3: one CTA per SM walks the same flat unit list
       const int sms = sm_count_cached();
       if (sms <= 0) return CA_ERR_CUDA;

@@ -58,7 +58,7 @@ class HeatmapAccumulator:
 
     def __init__(self, B, C, P, device, layer_indices, timesteps=None, softmax=True,
                  attention_norm="sparsemax", round_bf16=False, per_pair=False, buffer=None,
-                 pair_buffer=None):
+                 pair_buffer=None, pair_slot=None):
         """`per_pair=True` (BASELINE config 4) also keeps every selected pair's normalised map —
         the reference's `heatmaps[timesteps][:, layer_indices]` before the mean
         (concept_attention_pipeline.py:76-77) — in ONE fp32 buffer
@@ -89,7 +89,10 @@ class HeatmapAccumulator:
             else:
                 assert tuple(pair_buffer.shape) == shape and pair_buffer.dtype == torch.float32
                 self.pairs = pair_buffer.zero_()
-            self.pair_slot = torch.zeros(1, device=device, dtype=torch.int32)
+            # caller-owned like the buffers: a captured forward bakes this address in
+            self.pair_slot = (torch.zeros(1, device=device, dtype=torch.int32) if pair_slot is None
+                              else pair_slot.zero_())
+            assert self.pair_slot.dtype == torch.int32 and self.pair_slot.numel() == 1
 
     @property
     def per_pair(self):

@@ -80,7 +80,7 @@ def ln_modulate(x, mod0, mod1=None, split=None, shift_off=0, scale_off=None, out
     if out is None:
         out = torch.empty_like(x)
     scale_off = D if scale_off is None else scale_off
-    with _timed("K1a ln_modulate", 4 * B * N * D):
+    with _timed(f"K1a ln_modulate rows={B * N}", 4 * B * N * D):
         check(_cabi.load().ca_ln_modulate(
             x.data_ptr(), out.data_ptr(), B, N, D, mod0.data_ptr(),
             mod1.data_ptr() if mod1 is not None else None, N if split is None else split,
@@ -101,7 +101,7 @@ def gate_residual_ln_modulate(x, y, mod0, mod1=None, split=None, gate_off=0, shi
     assert y.stride(0) == N * y.stride(1) or B == 1
     if want_out and out is None:
         out = torch.empty_like(x)
-    with _timed("K1c gate_residual_ln_modulate", (8 if want_out else 6) * B * N * D):
+    with _timed(f"K1c gate_residual{'_ln_modulate' if want_out else ''} rows={B * N}", (8 if want_out else 6) * B * N * D):
         check(_cabi.load().ca_gate_residual_ln_modulate(
             x.data_ptr(), y.data_ptr(), y.stride(1), out.data_ptr() if want_out else None, B, N, D,
             mod0.data_ptr(), mod1.data_ptr() if mod1 is not None else None,
@@ -128,7 +128,7 @@ def qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope, H, want_q_pre=False):
     q_pre = torch.empty_like(q) if want_q_pre else None
     sb = scales_b if scales_b is not None else (None, None)
     Ntok = B * (Na + Nb)
-    with _timed("K1b qkv_prep", Ntok * (2 * 3 * H * 128 * 2 + 512 + (2 * H * 128 if want_q_pre else 0))):
+    with _timed(f"K1b qkv_prep{'+q_pre' if want_q_pre else ''} rows={Ntok}", Ntok * (2 * 3 * H * 128 * 2 + 512 + (2 * H * 128 if want_q_pre else 0))):
         check(_cabi.load().ca_qkv_prep(
             qkv_a.data_ptr(), qkv_a.stride(1), Na,
             qkv_b.data_ptr() if qkv_b is not None else None,
@@ -270,7 +270,7 @@ def heatmap_accumulate(img, con, acc, norm="softmax", round_bf16=False, per_head
     _req(acc, torch.float32, "acc")
     assert acc.shape == (B, C, P)
     K = nseg * seg_len
-    tm = _timed("K3+K4 heatmap_accumulate", B * (2 * P * K + 2 * C * K + (8 if pair is None else 12) * C * P))
+    tm = _timed(f"K3+K4 heatmap_accumulate {'cross' if per_head else 'output'} space rows={B * P}", B * (2 * P * K + 2 * C * K + (8 if pair is None else 12) * C * P))
     if pair is None:
         with tm:
             check(_cabi.load().ca_heatmap_accumulate(

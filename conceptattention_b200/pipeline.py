@@ -100,21 +100,22 @@ class FluxGenerator:
         adds the [Nt_sel, L_sel, 2, B, C, P] fp32 per-(timestep, layer) buffer (config 4:
         28 x 19 x 2 x 20 x 4096 x 4 B = 349 MB, where the reference stacks 26.8 GB of vectors,
         flux/src/flux/sampling.py:146-150)."""
-        def owned(key, shape):
+        def owned(key, shape, dtype=torch.float32):
             buf = self._acc_buffers.get(key)
             if buf is None:
-                if len(self._acc_buffers) >= 6:
+                if len(self._acc_buffers) >= 8:
                     self._acc_buffers.pop(next(iter(self._acc_buffers)))
-                buf = self._acc_buffers[key] = torch.empty(shape, device=self.device, dtype=torch.float32)
+                buf = self._acc_buffers[key] = torch.empty(shape, device=self.device, dtype=dtype)
             return buf
-        pairs = None
+        pairs = slot = None
         if per_pair:
             nt = len(set(int(t) for t in timesteps)) if timesteps is not None else 1
             nl = len(set(int(l) for l in layer_indices))
             pairs = owned(("pairs", nt, nl, B, C, P), (nt, nl, 2, B, C, P))
+            slot = owned(("pair_slot",), (1,), torch.int32)
         return HeatmapAccumulator(B, C, P, self.device, layer_indices, timesteps, softmax,
                                   attention_norm, round_bf16, per_pair=per_pair,
-                                  buffer=owned((B, C, P), (2, B, C, P)), pair_buffer=pairs)
+                                  buffer=owned((B, C, P), (2, B, C, P)), pair_buffer=pairs, pair_slot=slot)
 
     @torch.inference_mode()
     def prepare_inputs(self, prompt, concepts, latents):
