@@ -1836,6 +1836,8 @@ attn_v6_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
+#include "k2_attention_v7.cuh"
+
 // CA_ATTN_NEITHER: concept_attn = concept_v  (modified_double_stream_block.py:157-159),
 // i.e. a head-merge copy of the concept rows of V.
 __global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnParams p) {
@@ -2020,7 +2022,17 @@ extern "C" ca_status ca_joint_attention_ws(const void* q, const void* k, const v
     }
     const int64_t ctas = (int64_t)p.n_dp + 2 * p.sk_sms + p.n_concept;
     if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
-    if (ctas > 0 && g_attention_impl >= 30 && g_attention_impl <= 32 && pl.sk_sms == 0) {
+    if (ctas > 0 && g_attention_impl >= 40 && g_attention_impl <= 45 && pl.sk_sms == 0) {
+      // v7 (P through shared memory, S freed when loaded): 40 = every 4th pair on the polynomial,
+      // 41 = all MUFU, 42 = every 2nd;  v10 = v7 with the MMA issue split over three threads: 43 / 44 / 45
+      const int smem = (int)sizeof(SmemV7) + 1024;
+      auto kern = g_attention_impl == 40 ? attn_v7_kernel<4, false> : g_attention_impl == 41 ? attn_v7_kernel<0, false>
+                : g_attention_impl == 42 ? attn_v7_kernel<2, false> : g_attention_impl == 43 ? attn_v7_kernel<4, true>
+                : g_attention_impl == 44 ? attn_v7_kernel<0, true> : attn_v7_kernel<2, true>;
+      CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      kern<<<(unsigned)ctas, 384, smem, st>>>(tmq, tmk, tmv, p);
+      CA_LAUNCH_CHECK();
+    } else if (ctas > 0 && g_attention_impl >= 30 && g_attention_impl <= 32 && pl.sk_sms == 0) {
       // v6 (thread-per-row softmax, S double-buffered in 64-key chunks): 30 = every 4th pair on the
       // polynomial, 31 = all MUFU, 32 = every 2nd
       const int smem = (int)sizeof(SmemV6) + 1024;

@@ -1,0 +1,353 @@
+// K2 v7 / v10 — included by k2_attention.cu inside namespace ca (uses its tile constants, UnitV1,
+// decode_unit, key_tile, exp2_poly2, use_poly, store_out_row).
+//
+// v7: v5's thread-per-row softmax with P handed to the tensor core through SHARED memory instead
+// of over the S columns in TMEM, so that the score buffer of a query tile is free the moment the
+// softmax warps have pulled S_t(j) into registers.
+//
+// Why (profiles/r02_k2_stalls.md, profiles/r02_umma_rate.md): in v3/v5 P_t overlays S_t, so
+// S_t(j+1) = Q_t K(j+1)^T cannot be issued before O_t += P_t(j) V(j) has read P — the per-tile chain
+// is softmax -> PV -> QK -> softmax and a key step costs T_softmax + 1024 tensor cycles (measured
+// 3100 cycles, tensor pipe 66 % busy, softmax warps 36 % of their time on s_full).  A second S
+// buffer per tile does not fit TMEM (S0 S1 O0 O1 = 512 columns) and halving the key chunk does not
+// help: one tcgen05.mma costs at least 48 cycles, so eight N=64 MMAs take 384 cycles, not 256 (v6).
+// Here the chain is cut instead: QK_t(j+2) is issued while softmax_t works on step j+1, the softmax
+// never waits for a QK, and the tensor pipe only needs P_t(j) (two 64-key halves, one mbarrier
+// each) to run PV.  The SS form of PV reads P (A operand, K-major SW128, the Q-tile layout) from
+// smem; tcgen05.mma runs SS and TS at the same 64 cycles per N=128 K=16 step.
+//
+// Shared memory: Q 2 x 32 KB, P 2 x 32 KB, 3 K/V stages x 32 KB (224 KB).  Ring order = issue
+// order: K0 K1 | V0 K2 | V1 K3 | ...  (K runs two key steps ahead of V).
+// TMEM map as v1: S0 S1 O0 O1.
+
+constexpr int kV7Stages = 3;
+
+struct SmemV7 {
+  uint8_t q[2][kTileBytes];
+  uint8_t p[2][kTileBytes];
+  uint8_t kv[kV7Stages][kTileBytes];
+  uint64_t q_full[2], kv_full[kV7Stages], kv_empty[kV7Stages];
+  uint64_t s_full[2], s_free[2], p_full[2][2], pv_done[2], o_done;
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void v7_producer(SmemV7& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
+                                            const CUtensorMap* tmv, const UnitV1& u, int bh) {
+  int item = 0;
+  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
+    mbar_expect_tx(bar, kTileBytes);
+    tma_load_3d(dst, tm, bar, 0, row0, bh);
+    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+  };
+  auto load_kv = [&](const CUtensorMap* tm, int j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+    const int slot = item % kV7Stages;
+    mbar_wait(&sm.kv_empty[slot], ((item / kV7Stages) & 1) ^ 1);
+    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    ++item;
+  };
+  const int n = u.n_local;
+  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
+  load_kv(tmk, 0);
+  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
+  if (n > 1) load_kv(tmk, 1);
+  for (int j = 0; j < n; ++j) {
+    load_kv(tmv, j);
+    if (j + 2 < n) load_kv(tmk, j + 2);
+  }
+}
+
+// tcgen05.mma issue.  kRole = -1: ONE thread issues everything in ring order (v7).
+// kRole = 0 / 1 / 2: the issue is split over three threads — 0: S_t = Q_t K^T for both tiles,
+// 1: O_0 += P_0 V, 2: O_1 += P_1 V (v10).  The accumulators are disjoint per thread and every
+// cross-thread dependency already goes through an mbarrier; a K/V ring slot is then released by two
+// commit arrivals (two from the QK thread for a K tile, one from each PV thread — or two from PV_0
+// in a one-tile CTA — for a V tile).
+template <int kRole>
+__device__ __forceinline__ void v7_mma(SmemV7& sm, uint32_t tmem, const UnitV1& u) {
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  constexpr bool kSplit = kRole >= 0;
+  constexpr bool kDoQk = kRole <= 0;
+  const uint64_t dq = make_smem_desc(smem_u32(sm.q[0]), 16, 1024);
+  const uint64_t dp = make_smem_desc(smem_u32(sm.p[0]), 16, 1024);              // P tile: K-major
+  const uint64_t dk = make_smem_desc(smem_u32(sm.kv[0]), 16, 1024);             // K tile: K-major
+  const uint64_t dv = make_smem_desc(smem_u32(sm.kv[0]), kHalfBytes, 1024);     // V tile: MN-major
+  const bool two = u.n_q == 2;
+  const int n = u.n_local;
+  if (kRole == 2 && !two) return;
+  auto kv_wait = [&](int item) {
+    const int slot = item % kV7Stages;
+    mbar_wait(&sm.kv_full[slot], (item / kV7Stages) & 1);
+    return slot;
+  };
+  auto qk = [&](int t, int kslot, int jj) {               // S_t(jj) = Q_t K^T
+    if (jj == 0) mbar_wait(&sm.q_full[t], 0);
+    else mbar_wait(&sm.s_free[t], (jj - 1) & 1);          // S_t(jj-1) is in the softmax registers
+    tc_fence_after();
+    const uint64_t qa = dq + (uint64_t)(t * (kTileBytes >> 4)), ka = dk + (uint64_t)(kslot * (kTileBytes >> 4));
+#pragma unroll
+    for (int kk = 0; kk < kD / 16; ++kk) {
+      const uint32_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+      mma_ss(tmem + t * 128, qa + off, ka + off, idesc_qk, kk > 0);
+    }
+    mma_commit(&sm.s_full[t]);
+  };
+  auto pv = [&](int t, int vslot, int j) {               // O_t (+)= P_t V in two key halves
+    const uint64_t pa = dp + (uint64_t)(t * (kTileBytes >> 4)), va = dv + (uint64_t)(vslot * (kTileBytes >> 4));
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      mbar_wait(&sm.p_full[t][hf], j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 4 * hf; kk < 4 * hf + 4; ++kk) {
+        const uint32_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+        mma_ss(tmem + 256 + t * 128, pa + off, va + (uint64_t)(kk * (2048 >> 4)), idesc_pv, j > 0 || kk > 0);
+      }
+    }
+    mma_commit(&sm.pv_done[t]);
+  };
+  auto release = [&](int slot, int arrivals) {
+    mma_commit(&sm.kv_empty[slot]);
+    if (arrivals == 2) mma_commit(&sm.kv_empty[slot]);
+  };
+  // Every role walks the ring order K0 K1 | V0 K2 | V1 K3 | ... and acts on its own items.
+  int item = 0;
+  if (kDoQk) {
+    const int ks = kv_wait(item);
+    qk(0, ks, 0);
+    if (two) qk(1, ks, 0);
+    release(ks, kSplit ? 2 : 1);
+  }
+  ++item;
+  if (n > 1) {
+    if (kDoQk) {
+      const int ks = kv_wait(item);
+      qk(0, ks, 1);
+      if (two) qk(1, ks, 1);
+      release(ks, kSplit ? 2 : 1);
+    }
+    ++item;
+  }
+#pragma unroll 1
+  for (int j = 0; j < n; ++j) {
+    const bool has_k = j + 2 < n;
+    if (!kSplit) {
+      const int vs = kv_wait(item);
+      tc_fence_after();
+      pv(0, vs, j);
+      int ks = 0;
+      if (has_k) { ks = kv_wait(item + 1); qk(0, ks, j + 2); }
+      if (two) pv(1, vs, j);
+      release(vs, 1);
+      if (has_k) {
+        if (two) qk(1, ks, j + 2);
+        release(ks, 1);
+      }
+    } else if (kRole == 0) {
+      if (has_k) {
+        const int ks = kv_wait(item + 1);
+        qk(0, ks, j + 2);
+        if (two) qk(1, ks, j + 2);
+        release(ks, 2);
+      }
+    } else {
+      const int vs = kv_wait(item);
+      tc_fence_after();
+      pv(kRole - 1, vs, j);
+      release(vs, two ? 1 : 2);
+    }
+    item += has_k ? 2 : 1;
+  }
+  if (kRole != 0) mma_commit(&sm.o_done);
+}
+
+template <int kPolyEvery>
+__device__ __forceinline__ void v7_softmax(SmemV7& sm, uint32_t tmem, const UnitV1& u,
+                                           const AttnParams& p, int t, int b, int h) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const uint32_t t_s = tmem + t * 128 + lane_off, t_o = tmem + 256 + t * 128 + lane_off;
+  const float scale = p.scale_log2;
+  const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+  // P_t row of this thread in the K-major SW128 tile: 16-byte chunk c of 64-key block hf lives at
+  // hf * 16 KB + row * 128 + ((c ^ (row & 7)) << 4)
+  const uint32_t p_row = smem_u32(sm.p[t]) + (uint32_t)row * 128u;
+  const uint32_t p_xor = (uint32_t)(row & 7) << 4;
+  // the only ragged key tiles are the last of each key segment
+  const int n_local = u.n_local;
+  const int n1 = u.n_tiles - u.n0;
+  const int jr0 = u.n0 - 1 - u.j_begin, jr1 = u.n_tiles - 1 - u.j_begin;
+  const int vr0 = u.n0 > 0 ? (u.ks.e0 - u.ks.s0) - (u.n0 - 1) * kBN : kBN;
+  const int vr1 = n1 > 0 ? (u.ks.e1 - u.ks.s1) - (n1 - 1) * kBN : kBN;
+  float m_used = -INFINITY, l_sum = 0.f;
+
+#pragma unroll 1
+  for (int j = 0; j < n_local; ++j) {
+    const int valid = j == jr0 ? vr0 : (j == jr1 && n1 > 0) ? vr1 : kBN;
+    mbar_wait(&sm.s_full[t], j & 1);
+    tc_fence_after();
+    uint32_t s[kBN];
+    tmem_ld32(t_s, s);
+    tmem_ld32(t_s + 32, s + 32);
+    tmem_ld32(t_s + 64, s + 64);
+    tmem_ld32(t_s + 96, s + 96);
+    tmem_wait_ld32(s);
+    tmem_wait_ld32(s + 32);
+    tmem_wait_ld32(s + 64);
+    tmem_wait_ld32(s + 96);
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.s_free[t]);             // S_t may be overwritten by QK_t(j+1)
+    if (valid < kBN) {                                      // ragged last tile of a key segment
+#pragma unroll
+      for (int i = 0; i < kBN; ++i) if (i >= valid) s[i] = 0xff800000u;   // -inf
+    }
+    // row max: four independent FMNMX3 chains
+    float mc[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) mc[c] = __uint_as_float(s[c]);
+#pragma unroll
+    for (int i = 4; i < kBN; i += 8) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        mc[c] = fmaxf(fmaxf(mc[c], __uint_as_float(s[i + c])), __uint_as_float(s[(i + 4 + c) & (kBN - 1)]));
+    }
+    const float mx = fmaxf(fmaxf(mc[0], mc[1]), fmaxf(mc[2], mc[3]));
+    const bool grow = (mx - m_used) * scale > kRescaleThreshold;   // true on the first tile
+    const float m_new = grow ? mx : m_used;
+    bool pv_waited = j == 0;
+    if (j > 0 && __any_sync(0xffffffffu, grow)) {
+      // rare (lazy threshold): rescale O_t once PV_t(j-1) has landed
+      mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+      tc_fence_after();
+      pv_waited = true;
+      const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
+      l_sum *= alpha;
+#pragma unroll 1
+      for (int c = 0; c < kD; c += 8) {
+        uint32_t rc[8];
+        tmem_ld8(t_o + c, rc);
+        tmem_wait_ld8(rc);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+        tmem_st8(t_o + c, rc);
+      }
+      tmem_wait_st();
+    }
+    m_used = m_new;
+    const float mb = m_used * scale;
+    const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
+    uint64_t rsa = pk64(0.f, 0.f), rsb = pk64(0.f, 0.f);
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) {
+        uint32_t pk[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int e = 64 * hf + 8 * c8 + 2 * i;
+          const uint64_t x2 = fma2(pk64(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), scale2, nmb2);
+          float e0, e1;
+          if (use_poly<kPolyEvery>(c8 * 4 + i)) {
+            exp2_poly2(x2, e0, e1);
+          } else {
+            float x0, x1;
+            upk64(x2, x0, x1);
+            e0 = ex2(x0); e1 = ex2(x1);
+          }
+          if (i & 1) rsb = add2(rsb, pk64(e0, e1)); else rsa = add2(rsa, pk64(e0, e1));
+          pk[i] = pack2(e0, e1);
+        }
+        if (!pv_waited) {                                   // PV_t(j-1) has finished reading P_t
+          mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+          pv_waited = true;
+        }
+        st_shared_v4(p_row + hf * kHalfBytes + (((uint32_t)c8 << 4) ^ p_xor), pk[0], pk[1], pk[2], pk[3]);
+      }
+      fence_proxy_async_smem();                             // generic-proxy P writes -> async proxy (MMA)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.p_full[t][hf]);
+    }
+    {
+      float r0, r1, r2, r3;
+      upk64(rsa, r0, r1); upk64(rsb, r2, r3);
+      l_sum += (r0 + r1) + (r2 + r3);
+    }
+  }
+
+  // ---- epilogue: O_t / l -> bf16 "B L (H D)" ---------------------------------------
+  mbar_wait(&sm.o_done, 0);
+  tc_fence_after();
+  const float inv_l = 1.f / l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + c, r);
+    tmem_wait_ld32(r);
+    if (row < q_rows) {
+      float o[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+      store_out_row(p, b, h, q_row0 + row, o, inv_l, c, 32);
+    }
+  }
+}
+
+// kSplitIssue = false: v7 (warp 1 issues every MMA); true: v10 (warps 1, 2, 3 issue QK / PV_0 / PV_1).
+template <int kPolyEvery, bool kSplitIssue>
+__global__ void __launch_bounds__(384, 1)
+attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+               const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV7& sm = *reinterpret_cast<SmemV7*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const UnitV1 u = decode_unit(p, blockIdx.x);
+  if (u.n_local == 0) return;
+  const int bh = u.bh, b = bh / p.H, h = bh - b * p.H;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
+    for (int i = 0; i < kV7Stages; ++i) {
+      mbar_init(&sm.kv_full[i], 1);
+      mbar_init(&sm.kv_empty[i], kSplitIssue ? 2 : 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm.s_full[i], 1); mbar_init(&sm.s_free[i], 4); mbar_init(&sm.pv_done[i], 1);
+      mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
+    }
+    mbar_init(&sm.o_done, kSplitIssue ? u.n_q : 1);         // one commit per PV-issuing thread
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp < 4) {
+    // register pool of a 384-thread CTA: 384 x 168 = 64512 = 128 x 88 + 256 x 208
+    setmaxnreg_dec<88>();
+    if (warp == 0) {
+      if (elect_one()) v7_producer(sm, &tmq, &tmk, &tmv, u, bh);
+    } else if (!kSplitIssue) {
+      if (warp == 1 && elect_one()) v7_mma<-1>(sm, tmem, u);
+    } else if (warp == 1) {
+      if (elect_one()) v7_mma<0>(sm, tmem, u);
+    } else if (warp == 2) {
+      if (elect_one()) v7_mma<1>(sm, tmem, u);
+    } else {
+      if (elect_one()) v7_mma<2>(sm, tmem, u);
+    }
+  } else {
+    setmaxnreg_inc<208>();
+    const int t = (warp >> 2) - 1;
+    if (t < u.n_q) v7_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
