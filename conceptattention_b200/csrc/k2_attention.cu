@@ -2022,7 +2022,15 @@ extern "C" ca_status ca_joint_attention_ws(const void* q, const void* k, const v
     }
     const int64_t ctas = (int64_t)p.n_dp + 2 * p.sk_sms + p.n_concept;
     if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
-    if (ctas > 0 && g_attention_impl >= 40 && g_attention_impl <= 45 && pl.sk_sms == 0) {
+    if (ctas > 0 && g_attention_impl >= 50 && g_attention_impl <= 52 && pl.sk_sms == 0) {
+      // v11 (one score buffer shared by the two tiles, P in TMEM, five K/V stages): 50 / 51 / 52 as 40 / 41 / 42
+      const int smem = (int)sizeof(SmemV11) + 1024;
+      auto kern = g_attention_impl == 51 ? attn_v11_kernel<0> : g_attention_impl == 52 ? attn_v11_kernel<2>
+                                                              : attn_v11_kernel<4>;
+      CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      kern<<<(unsigned)ctas, 384, smem, st>>>(tmq, tmk, tmv, p);
+      CA_LAUNCH_CHECK();
+    } else if (ctas > 0 && g_attention_impl >= 40 && g_attention_impl <= 45 && pl.sk_sms == 0) {
       // v7 (P through shared memory, S freed when loaded): 40 = every 4th pair on the polynomial,
       // 41 = all MUFU, 42 = every 2nd;  v10 = v7 with the MMA issue split over three threads: 43 / 44 / 45
       const int smem = (int)sizeof(SmemV7) + 1024;

@@ -351,3 +351,282 @@ attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
+
+// =============================================================================
+// v11: ONE score buffer shared by the two query tiles, P_t back in TMEM next to it.
+//   TMEM  S [0,128) | P0 [128,192) | P1 [192,256) | O0 [256,384) | O1 [384,512)
+//   smem  Q 2 x 32 KB + FIVE K/V stages (v7's two P tiles cost it all but three, and removing the
+//         K/V reloads from a v7 launch makes it 9 % faster: the ring is too shallow)
+// The softmax warps free S as soon as it is in their registers (v7), so the two tiles alternate on
+// the one buffer: S0(j) -> load -> S1(j) -> load -> S0(j+1) ...; each S load (~300 cycles) sits
+// under the other tile's PV on the tensor pipe, and PV_t(j) never gates a QK.  Issue order
+//   QK0(0) QK1(0) | QK0(j+1) PV0(j) QK1(j+1) PV1(j) | ...      ring order K0 | K1 V0 | K2 V1 | ...
+// The k-th QK of the CTA waits for phase k-1 of the single s_free barrier.
+// =============================================================================
+constexpr int kV11Stages = 5;
+
+struct SmemV11 {
+  uint8_t q[2][kTileBytes];
+  uint8_t kv[kV11Stages][kTileBytes];
+  uint64_t q_full[2], kv_full[kV11Stages], kv_empty[kV11Stages];
+  uint64_t s_full[2], s_free, p_full[2][2], pv_done[2], o_done;
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void v11_producer(SmemV11& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
+                                             const CUtensorMap* tmv, const UnitV1& u, int bh) {
+  int item = 0;
+  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
+    mbar_expect_tx(bar, kTileBytes);
+    tma_load_3d(dst, tm, bar, 0, row0, bh);
+    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+  };
+  auto load_kv = [&](const CUtensorMap* tm, int j) {
+    int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
+    const int slot = item % kV11Stages;
+    mbar_wait(&sm.kv_empty[slot], ((item / kV11Stages) & 1) ^ 1);
+    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    ++item;
+  };
+  const int n = u.n_local;
+  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
+  load_kv(tmk, 0);
+  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
+  for (int j = 0; j < n; ++j) {
+    if (j + 1 < n) load_kv(tmk, j + 1);
+    load_kv(tmv, j);
+  }
+}
+
+__device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1& u) {
+  constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
+  constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
+  const uint64_t dq = make_smem_desc(smem_u32(sm.q[0]), 16, 1024);
+  const uint64_t dk = make_smem_desc(smem_u32(sm.kv[0]), 16, 1024);             // K tile: K-major
+  const uint64_t dv = make_smem_desc(smem_u32(sm.kv[0]), kHalfBytes, 1024);     // V tile: MN-major
+  const bool two = u.n_q == 2;
+  const int n = u.n_local;
+  int item = 0, n_qk = 0;
+  auto kv_wait = [&]() {
+    const int slot = item % kV11Stages;
+    mbar_wait(&sm.kv_full[slot], (item / kV11Stages) & 1);
+    ++item;
+    return slot;
+  };
+  auto qk = [&](int t, int kslot, int jj) {               // S = Q_t K(jj)^T
+    if (jj == 0) mbar_wait(&sm.q_full[t], 0);
+    if (n_qk > 0) mbar_wait(&sm.s_free, (n_qk - 1) & 1);  // the score tile before this one is in registers
+    tc_fence_after();
+    const uint64_t qa = dq + (uint64_t)(t * (kTileBytes >> 4)), ka = dk + (uint64_t)(kslot * (kTileBytes >> 4));
+#pragma unroll
+    for (int kk = 0; kk < kD / 16; ++kk) {
+      const uint32_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+      mma_ss(tmem, qa + off, ka + off, idesc_qk, kk > 0);
+    }
+    mma_commit(&sm.s_full[t]);
+    ++n_qk;
+  };
+  auto pv = [&](int t, int vslot, int j) {               // O_t (+)= P_t V in two key halves (P in TMEM)
+    const uint64_t va = dv + (uint64_t)(vslot * (kTileBytes >> 4));
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      mbar_wait(&sm.p_full[t][hf], j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 4 * hf; kk < 4 * hf + 4; ++kk)
+        mma_ts(tmem + 256 + t * 128, tmem + 128 + t * 64 + kk * 8, va + (uint64_t)(kk * (2048 >> 4)), idesc_pv,
+               j > 0 || kk > 0);
+    }
+    mma_commit(&sm.pv_done[t]);
+  };
+  int ks = kv_wait();
+  qk(0, ks, 0);
+  if (two) qk(1, ks, 0);
+  mma_commit(&sm.kv_empty[ks]);
+#pragma unroll 1
+  for (int j = 0; j < n; ++j) {
+    const bool has_k = j + 1 < n;
+    if (has_k) { ks = kv_wait(); qk(0, ks, j + 1); }
+    const int vs = kv_wait();
+    tc_fence_after();
+    pv(0, vs, j);
+    if (has_k) {
+      if (two) qk(1, ks, j + 1);
+      mma_commit(&sm.kv_empty[ks]);
+    }
+    if (two) pv(1, vs, j);
+    mma_commit(&sm.kv_empty[vs]);
+  }
+  mma_commit(&sm.o_done);
+}
+
+template <int kPolyEvery>
+__device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const UnitV1& u,
+                                            const AttnParams& p, int t, int b, int h) {
+  const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
+  const int row = warp_q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
+  const uint32_t t_s = tmem + lane_off, t_p = tmem + 128 + t * 64 + lane_off;
+  const uint32_t t_o = tmem + 256 + t * 128 + lane_off;
+  const float scale = p.scale_log2;
+  const int q_row0 = t ? u.q_row0[1] : u.q_row0[0], q_rows = t ? u.q_rows[1] : u.q_rows[0];
+  const int n_local = u.n_local;
+  const int n1 = u.n_tiles - u.n0;
+  const int jr0 = u.n0 - 1 - u.j_begin, jr1 = u.n_tiles - 1 - u.j_begin;
+  const int vr0 = u.n0 > 0 ? (u.ks.e0 - u.ks.s0) - (u.n0 - 1) * kBN : kBN;
+  const int vr1 = n1 > 0 ? (u.ks.e1 - u.ks.s1) - (n1 - 1) * kBN : kBN;
+  float m_used = -INFINITY, l_sum = 0.f;
+
+#pragma unroll 1
+  for (int j = 0; j < n_local; ++j) {
+    const int valid = j == jr0 ? vr0 : (j == jr1 && n1 > 0) ? vr1 : kBN;
+    mbar_wait(&sm.s_full[t], j & 1);
+    tc_fence_after();
+    uint32_t s[kBN];
+    tmem_ld32(t_s, s);
+    tmem_ld32(t_s + 32, s + 32);
+    tmem_ld32(t_s + 64, s + 64);
+    tmem_ld32(t_s + 96, s + 96);
+    tmem_wait_ld32(s);
+    tmem_wait_ld32(s + 32);
+    tmem_wait_ld32(s + 64);
+    tmem_wait_ld32(s + 96);
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.s_free);                // the score buffer goes to the other tile
+    if (valid < kBN) {
+#pragma unroll
+      for (int i = 0; i < kBN; ++i) if (i >= valid) s[i] = 0xff800000u;   // -inf
+    }
+    float mc[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) mc[c] = __uint_as_float(s[c]);
+#pragma unroll
+    for (int i = 4; i < kBN; i += 8) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        mc[c] = fmaxf(fmaxf(mc[c], __uint_as_float(s[i + c])), __uint_as_float(s[(i + 4 + c) & (kBN - 1)]));
+    }
+    const float mx = fmaxf(fmaxf(mc[0], mc[1]), fmaxf(mc[2], mc[3]));
+    const bool grow = (mx - m_used) * scale > kRescaleThreshold;
+    const float m_new = grow ? mx : m_used;
+    bool pv_waited = j == 0;
+    if (j > 0 && __any_sync(0xffffffffu, grow)) {
+      mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+      tc_fence_after();
+      pv_waited = true;
+      const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
+      l_sum *= alpha;
+#pragma unroll 1
+      for (int c = 0; c < kD; c += 8) {
+        uint32_t rc[8];
+        tmem_ld8(t_o + c, rc);
+        tmem_wait_ld8(rc);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) rc[i] = __float_as_uint(__uint_as_float(rc[i]) * alpha);
+        tmem_st8(t_o + c, rc);
+      }
+      tmem_wait_st();
+    }
+    m_used = m_new;
+    const float mb = m_used * scale;
+    const uint64_t scale2 = pk64(scale, scale), nmb2 = pk64(-mb, -mb);
+    uint64_t rsa = pk64(0.f, 0.f), rsb = pk64(0.f, 0.f);
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int e = 64 * hf + 2 * i;
+        const uint64_t x2 = fma2(pk64(__uint_as_float(s[e]), __uint_as_float(s[e + 1])), scale2, nmb2);
+        float e0, e1;
+        if (use_poly<kPolyEvery>(i)) {
+          exp2_poly2(x2, e0, e1);
+        } else {
+          float x0, x1;
+          upk64(x2, x0, x1);
+          e0 = ex2(x0); e1 = ex2(x1);
+        }
+        if (i & 1) rsb = add2(rsb, pk64(e0, e1)); else rsa = add2(rsa, pk64(e0, e1));
+        pk[i] = pack2(e0, e1);
+      }
+      if (!pv_waited) {                                     // PV_t(j-1) has finished reading P_t
+        mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+        tc_fence_after();
+        pv_waited = true;
+      }
+      tmem_st32(t_p + hf * 32, pk);                         // keys [64 hf, 64 hf + 64) of P_t
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.p_full[t][hf]);
+    }
+    {
+      float r0, r1, r2, r3;
+      upk64(rsa, r0, r1); upk64(rsb, r2, r3);
+      l_sum += (r0 + r1) + (r2 + r3);
+    }
+  }
+
+  mbar_wait(&sm.o_done, 0);
+  tc_fence_after();
+  const float inv_l = 1.f / l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + c, r);
+    tmem_wait_ld32(r);
+    if (row < q_rows) {
+      float o[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]);
+      store_out_row(p, b, h, q_row0 + row, o, inv_l, c, 32);
+    }
+  }
+}
+
+template <int kPolyEvery>
+__global__ void __launch_bounds__(384, 1)
+attn_v11_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+                const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV11& sm = *reinterpret_cast<SmemV11*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const UnitV1 u = decode_unit(p, blockIdx.x);
+  if (u.n_local == 0) return;
+  const int bh = u.bh, b = bh / p.H, h = bh - b * p.H;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
+    for (int i = 0; i < kV11Stages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm.s_full[i], 1); mbar_init(&sm.pv_done[i], 1);
+      mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
+    }
+    mbar_init(&sm.s_free, 4);
+    mbar_init(&sm.o_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp < 4) {
+    setmaxnreg_dec<88>();
+    if (warp == 0) {
+      if (elect_one()) v11_producer(sm, &tmq, &tmk, &tmv, u, bh);
+    } else if (warp == 1) {
+      if (elect_one()) v11_mma(sm, tmem, u);
+    }
+  } else {
+    setmaxnreg_inc<208>();
+    const int t = (warp >> 2) - 1;
+    if (t < u.n_q) v11_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
