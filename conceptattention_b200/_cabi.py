@@ -15,6 +15,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libconcept
 CA_OK = 0
 NORM = {"softmax": 0, "sparsemax": 1, "entmax15": 2, "none": 3}
 ATTN_BOTH, ATTN_CROSS_ONLY, ATTN_SELF_ONLY, ATTN_NEITHER = 0, 1, 2, 3
+K2_AUTO, K2_V3, K2_V7, K2_V11 = 0, 1, 2, 3
 MAX_CONCEPTS = 32            # CA_MAX_CONCEPTS
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
@@ -31,6 +32,8 @@ SIGNATURES = {
     "ca_joint_attention": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p],
     "ca_joint_attention_workspace_bytes": [_i] * 6,
     "ca_joint_attention_ws": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, C.c_size_t, _p],
+    "ca_joint_attention_workspace_bytes_ex": [_i] * 8,
+    "ca_joint_attention_ex": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, C.c_size_t, _i, _i, _p],
     "ca_heatmap_accumulate": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p],
     "ca_heatmap_accumulate_pair": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p,
                                    _i64, _p, _i, _p],
@@ -50,7 +53,8 @@ SIGNATURES = {
     "ca_heatmaps_from_vectors_host": [_p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _i, _i, _p],
 }
 _RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p,
-             "ca_joint_attention_workspace_bytes": C.c_size_t}
+             "ca_joint_attention_workspace_bytes": C.c_size_t,
+             "ca_joint_attention_workspace_bytes_ex": C.c_size_t}
 
 _lib = None
 
@@ -77,20 +81,10 @@ def load():
         fn = getattr(lib, name)          # AttributeError if the .so is stale
         fn.argtypes = argtypes
         fn.restype = _RESTYPES.get(name, C.c_int)
-    lib.ca_debug_set_attention_impl.argtypes = [_i]
-    lib.ca_debug_set_attention_impl.restype = None
-    lib.ca_debug_set_attention_streamk.argtypes = [_i]
-    lib.ca_debug_set_attention_streamk.restype = None
     lib.ca_debug_plan_streamk.argtypes = [_i, _i, _i, _i, _i, _p]
     lib.ca_debug_plan_streamk.restype = None
     lib.ca_debug_streamk_piece.argtypes = [_i, _i, _i, _i, _i, _p]
     lib.ca_debug_streamk_piece.restype = _i
-    lib.ca_debug_set_ln_impl.argtypes = [_i]
-    lib.ca_debug_set_ln_impl.restype = None
-    lib.ca_debug_set_heatmap_impl.argtypes = [_i]
-    lib.ca_debug_set_heatmap_impl.restype = None
-    lib.ca_debug_set_heatmap_split.argtypes = [_i]
-    lib.ca_debug_set_heatmap_split.restype = None
     _lib = lib
     return lib
 

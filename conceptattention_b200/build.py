@@ -21,7 +21,11 @@ SOURCES = ["ca_api.cu", "k1_prep.cu", "k2_attention.cu", "k3_heatmap.cu", "k3_he
            "k6_metrics.cu", "k7_seqpar.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-         "-Xcompiler", "-fPIC", "--use_fast_math", "-Xptxas", "-v"]
+         "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+# Only K2 is built with --use_fast_math (its exp2 / reciprocal are explicit approximations chosen in
+# the source, and flush-to-zero is wanted there); the HBM-bound kernels (K1, K3-K7) keep IEEE
+# division, sqrt and denormals so that their results do not depend on a compiler flag.
+EXTRA_FLAGS = {"k2_attention.cu": ["--use_fast_math"]}
 
 
 def _deps():
@@ -44,7 +48,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     def compile_one(src):
         s, o = os.path.join(CSRC, src), os.path.join(OBJ, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + deps):
-            r = subprocess.run([NVCC, *FLAGS, "-c", s, "-o", o], capture_output=True, text=True)
+            r = subprocess.run([NVCC, *FLAGS, *EXTRA_FLAGS.get(src, []), "-c", s, "-o", o], capture_output=True, text=True)
             if r.returncode != 0:
                 raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
             with open(o + ".ptxas.log", "w") as f:

@@ -147,7 +147,6 @@ ln_modulate_kernel(__nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restric
 // and single streams at B = 1), (1+scale) and shift are converted to fp32 once per CTA into
 // shared memory instead of once per row.  Same maths as ln_modulate_kernel: bit-identical.
 constexpr int kStreamWarps = 16;
-int g_ln_impl = 0;     // 0 = auto, 1 = one warp per row only, 2 = staged kernel wherever it applies
 
 template <int NCH, bool kResidual>
 __global__ void __launch_bounds__(kStreamWarps * 32, 1)
@@ -290,9 +289,8 @@ static ca_status launch_ln(void* x, const void* y, int64_t y_stride, void* out, 
   const int slots = (int)std::min<size_t>(2, budget / (kStreamWarps * (slot_bytes + 8) + 256));
   // Measured on B200 (scripts/bench_k1.py): the plain LN (one input stream) is faster in the
   // one-warp-per-row form (0.70 vs 0.60 of HBM at 16 K rows); the residual forms (two input
-  // streams, in-place update) are faster staged (0.74 / 0.79 vs 0.65 / 0.61).  impl 2 forces
-  // the staged kernel for every form (tests).
-  const bool stream = g_ln_impl == 2 || (g_ln_impl == 0 && kResidual);
+  // streams, in-place update) are faster staged (0.74 / 0.79 vs 0.65 / 0.61).
+  const bool stream = kResidual;
   if (stream && rows >= 1024 && slots >= 1 && nch <= 16) {
     static int sm_count = 0;
     if (sm_count == 0) {
@@ -423,7 +421,6 @@ qkv_prep_kernel(const __nv_bfloat16* __restrict__ qkv_a, int64_t stride_a, int N
 
 }  // namespace ca
 
-extern "C" void ca_debug_set_ln_impl(int impl) { ca::g_ln_impl = impl; }
 
 extern "C" ca_status ca_ln_modulate(const void* x, void* out, int B, int N, int D, const void* mod0,
                                     const void* mod1, int split, int64_t mod_stride,

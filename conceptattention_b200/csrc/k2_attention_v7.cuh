@@ -1,4 +1,4 @@
-// K2 v7 / v10 — included by k2_attention.cu inside namespace ca (uses its tile constants, UnitV1,
+// K2 v7 / v11 — included by k2_attention.cu inside namespace ca (uses its tile constants, UnitV1,
 // decode_unit, key_tile, exp2_poly2, use_poly, store_out_row).
 //
 // v7: v5's thread-per-row softmax with P handed to the tensor core through SHARED memory instead
@@ -57,28 +57,22 @@ __device__ __forceinline__ void v7_producer(SmemV7& sm, const CUtensorMap* tmq, 
   }
 }
 
-// tcgen05.mma issue.  kRole = -1: ONE thread issues everything in ring order (v7).
-// kRole = 0 / 1 / 2: the issue is split over three threads — 0: S_t = Q_t K^T for both tiles,
-// 1: O_0 += P_0 V, 2: O_1 += P_1 V (v10).  The accumulators are disjoint per thread and every
-// cross-thread dependency already goes through an mbarrier; a K/V ring slot is then released by two
-// commit arrivals (two from the QK thread for a K tile, one from each PV thread — or two from PV_0
-// in a one-tile CTA — for a V tile).
-template <int kRole>
+// One thread issues every tcgen05.mma of the CTA in ring order.  (Splitting the issue over three
+// threads — QK, PV_0, PV_1 — was tried: same time per launch, the issuing thread is not the limit.)
 __device__ __forceinline__ void v7_mma(SmemV7& sm, uint32_t tmem, const UnitV1& u) {
   constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
   constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
-  constexpr bool kSplit = kRole >= 0;
-  constexpr bool kDoQk = kRole <= 0;
   const uint64_t dq = make_smem_desc(smem_u32(sm.q[0]), 16, 1024);
   const uint64_t dp = make_smem_desc(smem_u32(sm.p[0]), 16, 1024);              // P tile: K-major
   const uint64_t dk = make_smem_desc(smem_u32(sm.kv[0]), 16, 1024);             // K tile: K-major
   const uint64_t dv = make_smem_desc(smem_u32(sm.kv[0]), kHalfBytes, 1024);     // V tile: MN-major
   const bool two = u.n_q == 2;
   const int n = u.n_local;
-  if (kRole == 2 && !two) return;
-  auto kv_wait = [&](int item) {
+  int item = 0;
+  auto kv_wait = [&]() {
     const int slot = item % kV7Stages;
     mbar_wait(&sm.kv_full[slot], (item / kV7Stages) & 1);
+    ++item;
     return slot;
   };
   auto qk = [&](int t, int kslot, int jj) {               // S_t(jj) = Q_t K^T
@@ -107,59 +101,29 @@ __device__ __forceinline__ void v7_mma(SmemV7& sm, uint32_t tmem, const UnitV1& 
     }
     mma_commit(&sm.pv_done[t]);
   };
-  auto release = [&](int slot, int arrivals) {
-    mma_commit(&sm.kv_empty[slot]);
-    if (arrivals == 2) mma_commit(&sm.kv_empty[slot]);
-  };
-  // Every role walks the ring order K0 K1 | V0 K2 | V1 K3 | ... and acts on its own items.
-  int item = 0;
-  if (kDoQk) {
-    const int ks = kv_wait(item);
-    qk(0, ks, 0);
-    if (two) qk(1, ks, 0);
-    release(ks, kSplit ? 2 : 1);
-  }
-  ++item;
-  if (n > 1) {
-    if (kDoQk) {
-      const int ks = kv_wait(item);
-      qk(0, ks, 1);
-      if (two) qk(1, ks, 1);
-      release(ks, kSplit ? 2 : 1);
-    }
-    ++item;
+#pragma unroll 1
+  for (int pre = 0; pre < 2 && pre < n; ++pre) {           // S_t(0), S_t(1)
+    const int ks = kv_wait();
+    qk(0, ks, pre);
+    if (two) qk(1, ks, pre);
+    mma_commit(&sm.kv_empty[ks]);
   }
 #pragma unroll 1
   for (int j = 0; j < n; ++j) {
     const bool has_k = j + 2 < n;
-    if (!kSplit) {
-      const int vs = kv_wait(item);
-      tc_fence_after();
-      pv(0, vs, j);
-      int ks = 0;
-      if (has_k) { ks = kv_wait(item + 1); qk(0, ks, j + 2); }
-      if (two) pv(1, vs, j);
-      release(vs, 1);
-      if (has_k) {
-        if (two) qk(1, ks, j + 2);
-        release(ks, 1);
-      }
-    } else if (kRole == 0) {
-      if (has_k) {
-        const int ks = kv_wait(item + 1);
-        qk(0, ks, j + 2);
-        if (two) qk(1, ks, j + 2);
-        release(ks, 2);
-      }
-    } else {
-      const int vs = kv_wait(item);
-      tc_fence_after();
-      pv(kRole - 1, vs, j);
-      release(vs, two ? 1 : 2);
+    const int vs = kv_wait();
+    tc_fence_after();
+    pv(0, vs, j);
+    int ks = 0;
+    if (has_k) { ks = kv_wait(); qk(0, ks, j + 2); }
+    if (two) pv(1, vs, j);
+    mma_commit(&sm.kv_empty[vs]);
+    if (has_k) {
+      if (two) qk(1, ks, j + 2);
+      mma_commit(&sm.kv_empty[ks]);
     }
-    item += has_k ? 2 : 1;
   }
-  if (kRole != 0) mma_commit(&sm.o_done);
+  mma_commit(&sm.o_done);
 }
 
 template <int kPolyEvery>
@@ -296,8 +260,7 @@ __device__ __forceinline__ void v7_softmax(SmemV7& sm, uint32_t tmem, const Unit
   }
 }
 
-// kSplitIssue = false: v7 (warp 1 issues every MMA); true: v10 (warps 1, 2, 3 issue QK / PV_0 / PV_1).
-template <int kPolyEvery, bool kSplitIssue>
+template <int kPolyEvery>
 __global__ void __launch_bounds__(384, 1)
 attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
@@ -311,15 +274,12 @@ attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
     mbar_init(&sm.q_full[0], 1); mbar_init(&sm.q_full[1], 1);
-    for (int i = 0; i < kV7Stages; ++i) {
-      mbar_init(&sm.kv_full[i], 1);
-      mbar_init(&sm.kv_empty[i], kSplitIssue ? 2 : 1);
-    }
+    for (int i = 0; i < kV7Stages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&sm.s_full[i], 1); mbar_init(&sm.s_free[i], 4); mbar_init(&sm.pv_done[i], 1);
       mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
     }
-    mbar_init(&sm.o_done, kSplitIssue ? u.n_q : 1);         // one commit per PV-issuing thread
+    mbar_init(&sm.o_done, 1);
     fence_barrier_init();
   }
   if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
@@ -333,14 +293,8 @@ attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
     setmaxnreg_dec<88>();
     if (warp == 0) {
       if (elect_one()) v7_producer(sm, &tmq, &tmk, &tmv, u, bh);
-    } else if (!kSplitIssue) {
-      if (warp == 1 && elect_one()) v7_mma<-1>(sm, tmem, u);
     } else if (warp == 1) {
-      if (elect_one()) v7_mma<0>(sm, tmem, u);
-    } else if (warp == 2) {
-      if (elect_one()) v7_mma<1>(sm, tmem, u);
-    } else {
-      if (elect_one()) v7_mma<2>(sm, tmem, u);
+      if (elect_one()) v7_mma(sm, tmem, u);
     }
   } else {
     setmaxnreg_inc<208>();

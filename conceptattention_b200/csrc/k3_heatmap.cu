@@ -136,7 +136,6 @@ __global__ void concept_linear_normalize_kernel(const __nv_bfloat16* __restrict_
     out[c * K + k] = __float2bfloat16_rn(bf16_round(__bfloat162float(in[c * K + k]) - mn) / s);
 }
 
-int g_heatmap_impl = 0;      // 0 = best available, 1 = force the SIMT kernel (debug / A-B tests)
 
 template <bool kLogitsOnly>
 static ca_status launch_heatmap(const HmArgs& a, cudaStream_t st) {
@@ -147,8 +146,8 @@ static ca_status launch_heatmap(const HmArgs& a, cudaStream_t st) {
   if (!aligned16(a.img) || !aligned16(a.con) || (a.isb | a.iss | a.isp | a.csb | a.css | a.csc) % 8)
     return CA_ERR_ALIGNMENT;
   if (a.B == 0 || a.P == 0) return CA_OK;
-  if (g_heatmap_impl != 1) {          // TMA/tcgen05 streaming variant when the shape fits it
-    const ca_status s = launch_heatmap_tc(a, kLogitsOnly, st);
+  {                                   // TMA/tcgen05 streaming variant when the shape fits it
+    const ca_status s = launch_heatmap_tc(a, kLogitsOnly, st);   // (seg_len % 64 == 0); else SIMT below
     if (s != CA_ERR_UNSUPPORTED) return s;
   }
   const size_t smem = (size_t)a.C * a.nseg * a.seg_len * 2;
@@ -172,7 +171,6 @@ static ca_status launch_heatmap(const HmArgs& a, cudaStream_t st) {
 
 }  // namespace ca
 
-extern "C" void ca_debug_set_heatmap_impl(int impl) { ca::g_heatmap_impl = impl; }
 
 extern "C" ca_status ca_heatmap_accumulate(const void* img, int64_t isb, int64_t iss, int64_t isp,
                                            const void* con, int64_t csb, int64_t css, int64_t csc,

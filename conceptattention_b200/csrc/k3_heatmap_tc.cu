@@ -199,7 +199,6 @@ static ca_status launch_tc(const CUtensorMap& tma, const CUtensorMap& tmb, const
   return CA_OK;
 }
 
-int g_heatmap_split = 0;      // debug: force the cluster split-K factor (0 = heuristic)
 
 ca_status launch_heatmap_tc(const HmArgs& a, bool logits_only, cudaStream_t st) {
   if (a.seg_len % 64 || a.C > 32 || a.P < 1 || a.B > 65535) return CA_ERR_UNSUPPORTED;
@@ -216,7 +215,6 @@ ca_status launch_heatmap_tc(const HmArgs& a, bool logits_only, cudaStream_t st) 
   const int smax = npad == 32 ? 4 : 8;
   while (S < smax && (int64_t)tiles * a.B * S < 128 && chunks % (2 * S) == 0 && chunks / (2 * S) >= 2)
     S *= 2;
-  if (g_heatmap_split > 0 && g_heatmap_split <= smax && chunks % g_heatmap_split == 0) S = g_heatmap_split;
   HmTcParams p{a.B, a.P, a.C, a.seg_len, chunks / S, a.norm, a.round_bf16, a.acc,
                a.pair, a.pair_stride, a.pair_slot, a.pair_slot_off};
 #define CA_TC(NP, CT)                                                                 \
@@ -231,4 +229,3 @@ ca_status launch_heatmap_tc(const HmArgs& a, bool logits_only, cudaStream_t st) 
 
 }  // namespace ca
 
-extern "C" void ca_debug_set_heatmap_split(int s) { ca::g_heatmap_split = s; }

@@ -217,9 +217,11 @@ def seq_unpack_out(recv, Pl, Tl, C, out=None):
     return attn_img, attn_tc
 
 
-def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_txtc=None):
+def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_txtc=None,
+                    impl=_cabi.K2_AUTO, plan_sms=0):
     """One-way joint attention over [img|txt|concept]; returns (out_img [B,P,H*128],
-    out_txtc [B,T+C,H*128])."""
+    out_txtc [B,T+C,H*128]).  impl / plan_sms: the per-call kernel and stream-K plan arguments of
+    ca_joint_attention_ex (K2_AUTO / 0 = what the product uses)."""
     for n, t in (("q", q), ("k", k), ("v", v)):
         _req(t, BF16, n)
     B, H, N, d = q.shape
@@ -230,16 +232,16 @@ def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_tx
         out_txtc = torch.empty(B, T + C, H * 128, device=q.device, dtype=BF16)
     lib = _cabi.load()
     # scratch for the stream-K tail (0 bytes when this shape is never split); torch owns it
-    ws_bytes = lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, mode)
+    ws_bytes = lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, impl, plan_sms)
     ws = torch.empty(ws_bytes, device=q.device, dtype=torch.uint8) if ws_bytes else None
     ev = None
     if ATTN_EVENTS is not None:
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
         ev[0].record()
-    check(lib.ca_joint_attention_ws(
+    check(lib.ca_joint_attention_ex(
         q.data_ptr(), k.data_ptr(), v.data_ptr(), B, H, P, T, C, mode,
         out_img.data_ptr() if P > 0 else None, out_txtc.data_ptr() if T + C > 0 else None,
-        ws.data_ptr() if ws is not None else None, ws_bytes, _stream(q)), "ca_joint_attention_ws")
+        ws.data_ptr() if ws is not None else None, ws_bytes, impl, plan_sms, _stream(q)), "ca_joint_attention_ex")
     if ev is not None:
         ev[1].record()
         ATTN_EVENTS.append((ev, B, P, T, C, H))

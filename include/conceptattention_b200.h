@@ -132,6 +132,25 @@ ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v,
                                 void* out_img, void* out_txtc,
                                 void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same, with the kernel and the tail plan chosen PER CALL (no process-wide switches):
+ *   impl     CA_K2_AUTO  the default of the two calls above: by key steps per query-tile unit,
+ *                        CA_K2_V11 up to 64 steps, CA_K2_V7 beyond (measured on B200)
+ *            CA_K2_V3    round-1 kernel: P overlays S in TMEM, two softmax warpgroups share a
+ *                        tile; the only one with the stream-K tail (uses `workspace`)
+ *            CA_K2_V7    P through shared memory, a tile's score buffer is free once loaded
+ *            CA_K2_V11   one score buffer shared by the two tiles, P in TMEM, five K/V stages
+ *   plan_sms 0 = plan the stream-K tail for the real SM count with the measured thresholds,
+ *            < 0 = never split, n > 0 = plan for n SMs (parity tests of the tail on any GPU)
+ * All kernels compute the same function to bf16 round-off; CA_ERR_INVALID_ARG for an unknown impl. */
+enum { CA_K2_AUTO = 0, CA_K2_V3 = 1, CA_K2_V7 = 2, CA_K2_V11 = 3 };
+size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,
+                                             int impl, int plan_sms);
+ca_status ca_joint_attention_ex(const void* q, const void* k, const void* v,
+                                int B, int H, int P, int T, int C, int mode,
+                                void* out_img, void* out_txtc,
+                                void* workspace, size_t workspace_bytes,
+                                int impl, int plan_sms, void* stream);
+
 /* ---- K3+K4: heatmap logits + normalise over concepts + accumulate -----------
  * logits[b,c,p] = sum_{s<nseg} sum_{j<seg_len} img[b,s,p,j] * con[b,s,c,j]
  * where element (b,s,p,j) sits at img + b*img_stride_b + s*img_stride_s +

@@ -87,15 +87,14 @@ def bench_sdpa(name, B, H, P, T, C, iters, pk):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--sdpa", action="store_true", help="also time the reference's SDPA calls on the same shapes")
-    ap.add_argument("--impls", default="0,2,3")
+    ap.add_argument("--impls", default="0,1,2,3", help="CA_K2_* per-call kernel ids: 0 auto, 1 v3, 2 v7, 3 v11")
     ap.add_argument("--only", default="")
     ap.add_argument("--iters", type=int, default=20)
     args = ap.parse_args()
     pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
     lib = _cabi.load()
-    # CA_STREAMK=-1: never split the last wave (A/B against the default plan)
-    lib.ca_debug_set_attention_streamk(int(os.environ.get("CA_STREAMK", "0")))
+    plan_sms = int(os.environ.get("CA_STREAMK", "0"))   # -1: never split the last wave (v3 only)
     for name, B, H, P, T, C in SHAPES:
         if args.only not in name:
             continue
@@ -104,14 +103,13 @@ def main():
                 for _ in range(2)]
         flops = 4 * 128 * H * B * ((T + P) ** 2 + C * (C + P))
         for impl in [int(i) for i in args.impls.split(",")]:
-            lib.ca_debug_set_attention_impl(impl)
             for i in range(3):
-                ops.joint_attention(*sets[i % 2], P, T, C)
+                ops.joint_attention(*sets[i % 2], P, T, C, impl=impl, plan_sms=plan_sms)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for i in range(args.iters):
-                ops.joint_attention(*sets[i % 2], P, T, C)
+                ops.joint_attention(*sets[i % 2], P, T, C, impl=impl, plan_sms=plan_sms)
             e1.record()
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / args.iters
@@ -120,7 +118,6 @@ def main():
                               "P": P, "T": T, "C": C, "ms": round(ms, 4), "TFLOPs": round(tf, 1),
                               "frac_burst_peak": round(tf / pk["bf16_tflops"], 3),
                               "frac_sustained_peak": round(tf / pk["bf16_tflops_sustained"], 3)}), flush=True)
-        lib.ca_debug_set_attention_impl(0)
         del sets
         torch.cuda.empty_cache()
         if args.sdpa:

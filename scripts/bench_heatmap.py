@@ -30,8 +30,6 @@ def main():
     import argparse
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
-    ap.add_argument("--impls", default="0,1")
-    ap.add_argument("--splits", default="0")
     ap.add_argument("--shape", action="append", default=[], help="B,P,C,K extra shape")
     args = ap.parse_args()
     peak = 6650.0
@@ -70,11 +68,7 @@ def main():
         torch.cuda.synchronize()
         copy_us = e0.elapsed_time(e1) * 1e3 / (10 * nbuf)
         del src, dsts
-        for impl, split in [(int(i), int(sp)) for i in args.impls.split(",") for sp in args.splits.split(",")]:
-            if impl == 1 and split != int(args.splits.split(",")[0]):
-                continue
-            lib.ca_debug_set_heatmap_impl(impl)
-            lib.ca_debug_set_heatmap_split(split)
+        for impl, split in [(0, 0)]:        # the launcher picks kernel and split-K factor by shape
             for i in range(3 * nbuf):
                 ops.heatmap_accumulate(*pairs[i % nbuf], acc, "softmax", False, per_head=per_head)
             torch.cuda.synchronize()
@@ -93,8 +87,6 @@ def main():
                               "achieved_GBps": round(gbs, 1), "peak_GBps": peak,
                               "frac": round(gbs / peak, 3), "buffers_rotated": nbuf, "split": split,
                               "same_bytes_copy_us": round(copy_us, 2)}), flush=True)
-        lib.ca_debug_set_heatmap_impl(0)
-        lib.ca_debug_set_heatmap_split(0)
         del pairs, acc
         torch.cuda.empty_cache()
 

@@ -38,8 +38,6 @@ def main():
         peak = json.load(open(path))["hbm_gbs"]
     dev = "cuda:0"
     D, H = 3072, 24
-    # CA_LN_IMPL=1: force the one-warp-per-row LN kernels (A/B against the streaming ones)
-    _cabi.load().ca_debug_set_ln_impl(int(os.environ.get("CA_LN_IMPL", "0")))
     rows_out = []
 
     def report(name, shape, nbytes, sec):

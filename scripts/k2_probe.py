@@ -8,17 +8,14 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from conceptattention_b200 import _cabi, ops  # noqa: E402
+from conceptattention_b200 import ops  # noqa: E402
 
 impl, B, H, P, T, C = (int(a) for a in sys.argv[1:7])
 iters = int(sys.argv[7]) if len(sys.argv) > 7 else 20
-lib = _cabi.load()
 N = P + T + C
 q, k, v = (torch.randn(B, H, N, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
-lib.ca_debug_set_attention_impl(0)
-ri, rt = ops.joint_attention(q, k, v, P, T, C, 0)
-lib.ca_debug_set_attention_impl(impl)
+ri, rt = ops.joint_attention(q, k, v, P, T, C, 0, impl=1)
 for _ in range(iters):
-    oi, ot = ops.joint_attention(q, k, v, P, T, C, 0)
+    oi, ot = ops.joint_attention(q, k, v, P, T, C, 0, impl=impl)
 torch.cuda.synchronize()
 print("ok", sys.argv[1:7], float((oi.float() - ri.float()).abs().max()), float((ot.float() - rt.float()).abs().max()))

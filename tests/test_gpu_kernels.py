@@ -72,37 +72,39 @@ def test_gate_residual_ln_modulate(ops, B, N, D, split, want_out):
 @pytest.mark.parametrize("B,N,D,split", [(1, 4096, 3072, None), (2, 1111, 3072, 1000), (3, 700, 256, 650),
                                          (1, 1025, 1032, 7)])
 def test_ln_streaming_kernels_match_row_kernels_and_oracle(ops, B, N, D, split):
-    """Large token streams take the persistent TMA-staged kernels (rows >= 1024); they must
-    agree BIT FOR BIT with the one-warp-per-row kernels (same summation order) and, through
-    them, with the oracle: ragged row counts per CTA/warp, B > 1, the per-row modulation
-    switch at `split`, a strided y (column slice of a wider matrix), and the no-LN form."""
-    from conceptattention_b200 import _cabi
-    lib = _cabi.load()
+    """Large token streams take the persistent TMA-staged kernels (residual forms, rows >= 1024);
+    they must agree BIT FOR BIT with the one-warp-per-row kernels (same summation order) — reached
+    here by feeding the same rows in chunks of 256, which the launcher routes to the row kernels —
+    and with the oracle: ragged row counts per CTA/warp, B > 1, the per-row modulation switch at
+    `split`, a strided y (column slice of a wider matrix), and the no-LN form."""
     x, y = rnd(B, N, D, seed=11, scale=2.0).cuda(), rnd(B, N, 2 * D, seed=12).cuda()[:, :, D:]
     mod0, mod1 = rnd(B, 6 * D, seed=13, scale=0.5).cuda(), rnd(B, 6 * D, seed=14, scale=0.5).cuda()
     m1 = None if split is None else mod1
-    res = {}
-    for impl in (1, 2):
-        lib.ca_debug_set_ln_impl(impl)
-        try:
-            a = ops.ln_modulate(x, mod0, m1, split, 0, D)
-            xb = x.clone()
-            b = ops.gate_residual_ln_modulate(xb, y, mod0, m1, split, 2 * D, 3 * D, 4 * D)
-            xc = x.clone()
-            ops.gate_residual_ln_modulate(xc, y, mod0, m1, split, 5 * D, 0, 0, want_out=False)
-            torch.cuda.synchronize()
-        finally:
-            lib.ca_debug_set_ln_impl(0)
-        res[impl] = (a, b, xb, xc)
-    for got, ref in zip(res[2], res[1]):
-        assert torch.equal(got, ref)
+
+    def run(xs, ys, sp):
+        a = ops.ln_modulate(xs, mod0, None if sp is None else mod1, sp, 0, D)
+        xb = xs.clone()
+        b = ops.gate_residual_ln_modulate(xb, ys, mod0, None if sp is None else mod1, sp, 2 * D, 3 * D, 4 * D)
+        xc = xs.clone()
+        ops.gate_residual_ln_modulate(xc, ys, mod0, None if sp is None else mod1, sp, 5 * D, 0, 0, want_out=False)
+        return a, b, xb, xc
+
+    whole = run(x, y, split)
+    parts = []
+    for a0 in range(0, N, 256):
+        b0 = min(N, a0 + 256)
+        sp = None if split is None else min(max(split - a0, 0), b0 - a0)
+        parts.append(run(x[:, a0:b0].contiguous(), y[:, a0:b0], sp))
+    torch.cuda.synchronize()
+    for i, got in enumerate(whole):
+        assert torch.equal(got, torch.cat([pt[i] for pt in parts], dim=1)), i
     s_ = N if split is None else split
     xf = x.float().cpu()
     ref = torch.empty_like(xf)
     for m, sl in ((mod0, slice(0, s_)), (mod1, slice(s_, N))):
         mf = m.float().cpu()[:, None, :]
         ref[:, sl] = oracle.layer_norm_modulate(xf[:, sl], mf[..., :D], mf[..., D:2 * D])
-    close(res[2][0], ref, rtol=1e-2, atol=2e-2)
+    close(whole[0], ref, rtol=1e-2, atol=2e-2)
 
 
 # ---------------------------------------------------------------- K1b
@@ -188,16 +190,13 @@ def test_joint_attention_stream_k_tail(ops, B, H, P, T, C, sms):
     lib = _cabi.load()
     N = P + T + C
     q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((30, 1.5), (31, 1.0), (32, 1.0)))
-    try:
-        lib.ca_debug_set_attention_streamk(-1)
-        assert lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, 0) == 0
-        base = ops.joint_attention(q, k, v, P, T, C)
-        lib.ca_debug_set_attention_streamk(sms)
-        assert lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, 0) > 0, "plan did not split: pick other sizes"
-        runs = [ops.joint_attention(q, k, v, P, T, C) for _ in range(3)]
-        torch.cuda.synchronize()
-    finally:
-        lib.ca_debug_set_attention_streamk(0)
+    V3 = _cabi.K2_V3                                   # the kernel with the stream-K tail, chosen per call
+    assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, 0, V3, -1) == 0
+    assert lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, 0) == 0      # default kernels never split
+    base = ops.joint_attention(q, k, v, P, T, C, impl=V3, plan_sms=-1)
+    assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, 0, V3, sms) > 0, "plan did not split: pick other sizes"
+    runs = [ops.joint_attention(q, k, v, P, T, C, impl=V3, plan_sms=sms) for _ in range(3)]
+    torch.cuda.synchronize()
     ri, rt = _attention_oracle(q.float().cpu(), k.float().cpu(), v.float().cpu(), P, T, C, 0)
     for got, ref, b in zip(runs[0], (ri, rt), base):
         close(got, ref, rtol=2e-2, atol=1e-2)
@@ -206,55 +205,27 @@ def test_joint_attention_stream_k_tail(ops, B, H, P, T, C, sms):
         assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1])
 
 
+@pytest.mark.parametrize("impl", ["V3", "V7", "V11"])
 @pytest.mark.parametrize("B,H,P,T,C,mode", [(1, 2, 1024, 256, 32, 0), (2, 3, 256, 256, 4, 0), (1, 2, 2200, 200, 5, 0),
-                                            (1, 1, 200, 100, 1, 0), (1, 2, 144, 72, 3, 1)])
-def test_joint_attention_optimistic_max_is_bit_identical(ops, B, H, P, T, C, mode):
-    """impl 13 starts each tile's exp2 with the row max already in use and checks the exchanged
-    max afterwards, redoing the tile when it grew past the lazy-rescale threshold: same maths
-    in every case, so the output must equal the plain kernel's bit for bit — also with scores
-    that keep growing along the keys (forces the redo path on many tiles)."""
+                                            (1, 1, 200, 100, 1, 0), (1, 2, 144, 72, 3, 1), (1, 2, 100, 20, 3, 2),
+                                            (2, 2, 0, 130, 0, 0), (8, 24, 256, 128, 2, 0)])
+def test_joint_attention_every_kernel_matches_oracle(ops, impl, B, H, P, T, C, mode):
+    """ca_joint_attention_ex with each kernel named per call (CA_K2_V3 / V7 / V11): same function to
+    bf16 round-off — also with scores that keep growing along the keys (forces the lazy O rescale
+    on many tiles), one-tile units, ragged key tiles in both key segments, and more concept
+    units than SMs (8 x 24 of them: CTAs that follow a one-tile CTA on the same SM)."""
     from conceptattention_b200 import _cabi
-    lib = _cabi.load()
+    which = getattr(_cabi, "K2_" + impl)
     N = P + T + C
     q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((40, 1.5), (41, 1.0), (42, 1.0)))
     ramp = torch.linspace(0.2, 6.0, N, device="cuda").view(1, 1, N, 1)          # later keys score higher
-    for kk in (k, (k.float() * ramp).to(BF16)):
-        outs = {}
-        for impl in (0, 13):
-            lib.ca_debug_set_attention_impl(impl)
-            try:
-                outs[impl] = ops.joint_attention(q, kk, v, P, T, C, mode)
-                torch.cuda.synchronize()
-            finally:
-                lib.ca_debug_set_attention_impl(0)
-        assert torch.equal(outs[0][0], outs[13][0]) and torch.equal(outs[0][1], outs[13][1])
-    ri, rt = _attention_oracle(q.float().cpu(), k.float().cpu(), v.float().cpu(), P, T, C, mode)
-    close(outs[13][0] if False else ops.joint_attention(q, k, v, P, T, C, mode)[0], ri, rtol=2e-2, atol=1e-2)
-
-
-@pytest.mark.parametrize("B,H,P,T,C,mode,plan", [(1, 1, 200, 100, 1, 0, 0), (1, 2, 144, 72, 3, 1, 0),
-                                                 (2, 24, 1024, 256, 4, 0, 0), (1, 2, 2000, 200, 3, 0, 7),
-                                                 (1, 2, 2200, 200, 5, 0, 24)])
-def test_joint_attention_persistent_form_is_bit_identical(ops, B, H, P, T, C, mode, plan):
-    """impl 14 (opt-in): one CTA per SM walks the same unit list with running barrier parities; the
-    per-unit maths and the stream-K merge order are unchanged, so outputs must equal the default
-    kernel's bit for bit — with fewer units than SMs, several units per SM (2 x 24 heads x 5 pairs
-    + 48 concept units on 148 SMs) and forced stream-K plans."""
-    from conceptattention_b200 import _cabi
-    lib = _cabi.load()
-    N = P + T + C
-    q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((50, 1.5), (51, 1.0), (52, 1.0)))
-    outs = {}
-    lib.ca_debug_set_attention_streamk(plan)
-    try:
-        for impl in (0, 14):
-            lib.ca_debug_set_attention_impl(impl)
-            outs[impl] = ops.joint_attention(q, k, v, P, T, C, mode)
-            torch.cuda.synchronize()
-    finally:
-        lib.ca_debug_set_attention_impl(0)
-        lib.ca_debug_set_attention_streamk(0)
-    assert torch.equal(outs[0][0], outs[14][0]) and torch.equal(outs[0][1], outs[14][1])
+    for kk in ((k,) if B * H > 8 else (k, (k.float() * ramp).to(BF16))):
+        oi, ot = ops.joint_attention(q, kk, v, P, T, C, mode, impl=which)
+        torch.cuda.synchronize()
+        ri, rt = _attention_oracle(q.float().cpu(), kk.float().cpu(), v.float().cpu(), P, T, C, mode)
+        if P:
+            close(oi, ri, rtol=2e-2, atol=1e-2)
+        close(ot, rt, rtol=2e-2, atol=1e-2)
 
 
 def test_joint_attention_one_way(ops):
