@@ -699,15 +699,16 @@ extern "C" size_t ca_joint_attention_workspace_bytes(int B, int H, int P, int T,
 
 namespace ca {
 // cudaFuncSetAttribute once per kernel and process, not once per launch
-template <typename K> static ca_status launch_k2(K kern, int smem, int64_t ctas, cudaStream_t st,
+// (the kernel is a template VALUE: one `configured` flag per kernel, not per function type)
+template <auto kKern> static ca_status launch_k2(int smem, int64_t ctas, cudaStream_t st,
                                                  const CUtensorMap& tmq, const CUtensorMap& tmk,
                                                  const CUtensorMap& tmv, const AttnParams& p) {
   static bool configured = false;
   if (!configured) {
-    CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CA_CUDA_OK(cudaFuncSetAttribute(kKern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  kern<<<(unsigned)ctas, 384, smem, st>>>(tmq, tmk, tmv, p);
+  kKern<<<(unsigned)ctas, 384, smem, st>>>(tmq, tmk, tmv, p);
   CA_LAUNCH_CHECK();
   return CA_OK;
 }
@@ -763,9 +764,9 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
   if (ctas > 0) {
     // every kernel: polynomial exp2 on every 4th element pair (the MUFU / FMA-pipe balance point)
-    if (kernel == CA_K2_V11) s = launch_k2(attn_v11_kernel<4>, (int)sizeof(SmemV11) + 1024, ctas, st, tmq, tmk, tmv, p);
-    else if (kernel == CA_K2_V7) s = launch_k2(attn_v7_kernel<4>, (int)sizeof(SmemV7) + 1024, ctas, st, tmq, tmk, tmv, p);
-    else s = launch_k2(attn_v3_kernel<4>, (int)sizeof(SmemV1) + 1024, ctas, st, tmq, tmk, tmv, p);
+    if (kernel == CA_K2_V11) s = launch_k2<attn_v11_kernel<4>>((int)sizeof(SmemV11) + 1024, ctas, st, tmq, tmk, tmv, p);
+    else if (kernel == CA_K2_V7) s = launch_k2<attn_v7_kernel<4>>((int)sizeof(SmemV7) + 1024, ctas, st, tmq, tmk, tmv, p);
+    else s = launch_k2<attn_v3_kernel<4>>((int)sizeof(SmemV1) + 1024, ctas, st, tmq, tmk, tmv, p);
     if (s != CA_OK) return s;
   }
   if (C > 0 && mode == CA_ATTN_NEITHER) {

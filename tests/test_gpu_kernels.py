@@ -77,9 +77,9 @@ def test_ln_streaming_kernels_match_row_kernels_and_oracle(ops, B, N, D, split):
     here by feeding the same rows in chunks of 256, which the launcher routes to the row kernels —
     and with the oracle: ragged row counts per CTA/warp, B > 1, the per-row modulation switch at
     `split`, a strided y (column slice of a wider matrix), and the no-LN form."""
-    x, y = rnd(B, N, D, seed=11, scale=2.0).cuda(), rnd(B, N, 2 * D, seed=12).cuda()[:, :, D:]
+    x, yw = rnd(B, N, D, seed=11, scale=2.0).cuda(), rnd(B, N, 2 * D, seed=12).cuda()
+    y = yw[:, :, D:]
     mod0, mod1 = rnd(B, 6 * D, seed=13, scale=0.5).cuda(), rnd(B, 6 * D, seed=14, scale=0.5).cuda()
-    m1 = None if split is None else mod1
 
     def run(xs, ys, sp):
         a = ops.ln_modulate(xs, mod0, None if sp is None else mod1, sp, 0, D)
@@ -94,7 +94,7 @@ def test_ln_streaming_kernels_match_row_kernels_and_oracle(ops, B, N, D, split):
     for a0 in range(0, N, 256):
         b0 = min(N, a0 + 256)
         sp = None if split is None else min(max(split - a0, 0), b0 - a0)
-        parts.append(run(x[:, a0:b0].contiguous(), y[:, a0:b0], sp))
+        parts.append(run(x[:, a0:b0].contiguous(), yw[:, a0:b0].contiguous()[:, :, D:], sp))
     torch.cuda.synchronize()
     for i, got in enumerate(whole):
         assert torch.equal(got, torch.cat([pt[i] for pt in parts], dim=1)), i
