@@ -592,7 +592,29 @@ __global__ void concept_v_copy_kernel(const __nv_bfloat16* __restrict__ v, AttnP
 
 // ---- host side -------------------------------------------------------------------
 // [B*H, Ntot, 128] bf16 viewed as a 3-D tensor; box = 64 x box_rows x 1, 128B swizzle.
+// A descriptor depends only on (pointer, B*H, rows, box): the engine launches K2 57 times per
+// forward on the same few buffers, so the encoded maps are kept in a small per-thread table
+// (no locks, no cross-thread state) instead of three driver calls per launch.
 static ca_status make_qkv_tmap(CUtensorMap* m, const void* base, int BH, int Ntot, int box_rows) {
+  struct Entry { const void* base; int bh, n, box; CUtensorMap map; };
+  constexpr int kSlots = 16;
+  thread_local Entry cache[kSlots];
+  thread_local int used = 0, next = 0;
+  for (int i = 0; i < used; ++i)
+    if (cache[i].base == base && cache[i].bh == BH && cache[i].n == Ntot && cache[i].box == box_rows) {
+      *m = cache[i].map;
+      return CA_OK;
+    }
+  struct Store {
+    Entry* c; int* used; int* next; const void* base; int bh, n, box; const CUtensorMap* m; bool ok = false;
+    ~Store() {
+      if (!ok) return;
+      Entry& e = c[*next];
+      e.base = base; e.bh = bh; e.n = n; e.box = box; e.map = *m;
+      *next = (*next + 1) % kSlots;
+      if (*used < kSlots) ++*used;
+    }
+  } store{cache, &used, &next, base, BH, Ntot, box_rows, m};
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return CA_ERR_CUDA;
   const cuuint64_t dims[3] = {(cuuint64_t)kD, (cuuint64_t)Ntot, (cuuint64_t)BH};
@@ -603,9 +625,9 @@ static ca_status make_qkv_tmap(CUtensorMap* m, const void* base, int BH, int Nto
                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { g_last_cuda_error = (int)r; return CA_ERR_CUDA; }
+  store.ok = true;
   return CA_OK;
 }
-
 
 // Stream-K plan for the main units of one launch.  W units of n key steps each on S SMs: the
 // first floor(W/S)*S run whole (one CTA each); the remaining R < S would leave S-R SMs idle for a

@@ -130,10 +130,27 @@ def add_noise_to_image(encoded_image, num_steps=50, noise_timestep=49, seed=63, 
     return t * x + (1.0 - t) * encoded_image.to(x.dtype), ts[noise_timestep:]
 
 
-# plasma colormap, 10 anchor colours of the matplotlib table (linear interpolation in
-# between); used only when matplotlib is absent.
+# plasma colormap.  With matplotlib importable its own 256-entry table is used (exact reference
+# behaviour).  Without it (this image has no matplotlib and no network to fetch the table from) a
+# 256-entry LUT is built once from 10 anchor colours of the matplotlib table by linear
+# interpolation and LOOKED UP the way matplotlib does it (Colormap.__call__): index =
+# int(x * 256) clipped to 255, no interpolation between entries, NaN -> the "bad" colour (0, 0, 0).
 _PLASMA = [(13, 8, 135), (70, 3, 159), (114, 1, 168), (156, 23, 158), (189, 55, 134),
            (216, 87, 107), (237, 121, 83), (251, 159, 58), (253, 202, 38), (240, 249, 33)]
+_PLASMA_LUT = None
+
+
+def plasma_lut():
+    """uint8 [256,3] stand-in for matplotlib's plasma table (anchors exact, in between linear)."""
+    global _PLASMA_LUT
+    if _PLASMA_LUT is None:
+        import numpy as np
+        anchors = np.asarray(_PLASMA, dtype=np.float64)
+        pos = np.arange(256) / 255.0 * (len(anchors) - 1)
+        lo = np.floor(pos).astype(int).clip(0, len(anchors) - 2)
+        f = (pos - lo)[:, None]
+        _PLASMA_LUT = np.rint(anchors[lo] * (1 - f) + anchors[lo + 1] * f).astype(np.uint8)
+    return _PLASMA_LUT
 
 
 def apply_colormap(x01, cmap="plasma"):
@@ -143,8 +160,11 @@ def apply_colormap(x01, cmap="plasma"):
         import matplotlib.pyplot as plt
         return (plt.get_cmap(cmap)(x01)[:, :, :3] * 255).astype(np.uint8)
     except ImportError:
-        anchors = np.asarray(_PLASMA, dtype=np.float64) / 255.0
-        pos = np.clip(np.nan_to_num(x01), 0, 1) * (len(anchors) - 1)
-        lo = np.floor(pos).astype(int).clip(0, len(anchors) - 2)
-        f = (pos - lo)[..., None]
-        return ((anchors[lo] * (1 - f) + anchors[lo + 1] * f) * 255).astype(np.uint8)
+        if cmap != "plasma":
+            raise ValueError(f"cmap={cmap!r} needs matplotlib; only 'plasma' is built in")
+        x = np.asarray(x01, dtype=np.float64)
+        bad = np.isnan(x)
+        idx = np.clip((np.nan_to_num(x) * 256).astype(np.int64), 0, 255)
+        out = plasma_lut()[idx]
+        out[bad] = 0
+        return out
