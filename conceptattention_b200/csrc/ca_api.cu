@@ -43,31 +43,47 @@ extern "C" ca_status ca_heatmaps_from_vectors_host(const void* image_host, const
   const int64_t K = (int64_t)H * d;
   const size_t img_bytes = (size_t)B * P * K * 2, con_bytes = (size_t)B * C * K * 2;
   const size_t heat_bytes = (size_t)B * C * P * sizeof(float);
-  cudaStream_t st;
-  CA_CUDA_OK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  // two streams: `sc` copies pair i+1 into one buffer while `st` runs the kernel of pair i on the
+  // other; copied[s] / consumed[s] order the two users of buffer s
+  cudaStream_t st = nullptr, sc = nullptr;
+  cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
   void *dimg[2] = {nullptr, nullptr}, *dcon[2] = {nullptr, nullptr};
   float* dacc = nullptr;
   ca_status rc = CA_OK;
   auto cleanup = [&]() {
-    for (int i = 0; i < 2; ++i) { cudaFree(dimg[i]); cudaFree(dcon[i]); }
+    if (st) cudaStreamSynchronize(st);
+    if (sc) cudaStreamSynchronize(sc);
+    for (int i = 0; i < 2; ++i) {
+      cudaFree(dimg[i]); cudaFree(dcon[i]);
+      if (copied[i]) cudaEventDestroy(copied[i]);
+      if (consumed[i]) cudaEventDestroy(consumed[i]);
+    }
     cudaFree(dacc);
-    cudaStreamDestroy(st);
+    if (st) cudaStreamDestroy(st);
+    if (sc) cudaStreamDestroy(sc);
   };
 #define CA_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { cleanup(); return ca::cuda_fail(_e); } } while (0)
-  for (int i = 0; i < 2; ++i) { CA_TRY(cudaMalloc(&dimg[i], img_bytes)); CA_TRY(cudaMalloc(&dcon[i], con_bytes)); }
+  CA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  CA_TRY(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) {
+    CA_TRY(cudaMalloc(&dimg[i], img_bytes)); CA_TRY(cudaMalloc(&dcon[i], con_bytes));
+    CA_TRY(cudaEventCreateWithFlags(&copied[i], cudaEventDisableTiming));
+    CA_TRY(cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming));
+  }
   CA_TRY(cudaMalloc(&dacc, heat_bytes));
   CA_TRY(cudaMemsetAsync(dacc, 0, heat_bytes, st));
-  // double-buffered: the copy of pair i+1 is queued behind the kernel of pair i-1 on one stream;
-  // with pinned host memory the DMA engine overlaps it with the kernel of pair i.
   int it = 0;
   for (int ti = 0; ti < n_timesteps && rc == CA_OK; ++ti) {
     for (int li = 0; li < n_layers && rc == CA_OK; ++li, ++it) {
       const int64_t tl = (int64_t)timesteps[ti] * L + layers[li];
       const int s = it & 1;
+      if (it >= 2) CA_TRY(cudaStreamWaitEvent(sc, consumed[s], 0));   // the kernel of pair it-2 has read buffer s
       CA_TRY(cudaMemcpyAsync(dimg[s], (const char*)image_host + tl * img_bytes, img_bytes,
-                             cudaMemcpyHostToDevice, st));
+                             cudaMemcpyHostToDevice, sc));
       CA_TRY(cudaMemcpyAsync(dcon[s], (const char*)concept_host + tl * con_bytes, con_bytes,
-                             cudaMemcpyHostToDevice, st));
+                             cudaMemcpyHostToDevice, sc));
+      CA_TRY(cudaEventRecord(copied[s], sc));
+      CA_TRY(cudaStreamWaitEvent(st, copied[s], 0));
       if (per_head)      // [B,H,P,d] / [B,H,C,d]
         rc = ca_heatmap_accumulate(dimg[s], (int64_t)H * P * d, (int64_t)P * d, d, dcon[s],
                                    (int64_t)H * C * d, (int64_t)C * d, d, H, d, B, P, C, norm,
@@ -75,6 +91,7 @@ extern "C" ca_status ca_heatmaps_from_vectors_host(const void* image_host, const
       else               // [B,P,K] / [B,C,K]
         rc = ca_heatmap_accumulate(dimg[s], (int64_t)P * K, 0, K, dcon[s], (int64_t)C * K, 0, K, 1,
                                    (int)K, B, P, C, norm, round_bf16, dacc, st);
+      if (rc == CA_OK) CA_TRY(cudaEventRecord(consumed[s], st));
     }
   }
   if (rc == CA_OK)
