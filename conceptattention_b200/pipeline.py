@@ -273,10 +273,13 @@ class ConceptAttentionFluxPipeline:
             if gen.ae is None:
                 raise RuntimeError("encode_image(PIL image) needs a VAE (ae=...); offline pass "
                                    "latents [B,16,h/8,w/8] instead")
-            arr = torch.from_numpy(np.asarray(image.convert("RGB"))).permute(2, 0, 1).float() / 255.0
+            # uint8 HWC goes to the device as it is; scale, resize (nearest, as torch's
+            # F.interpolate default in segmentation.py:115-131) and VAE encode run there
+            arr = torch.from_numpy(np.asarray(image.convert("RGB"))).to(dev, non_blocking=True)
+            arr = arr.permute(2, 0, 1).float() / 255.0
             arr = torch.nn.functional.interpolate((2.0 * arr - 1.0)[None], (height, width))
             with torch.autocast(device_type=dev.type, dtype=torch.bfloat16):
-                clean = gen.ae.encode(arr.to(dev))
+                clean = gen.ae.encode(arr)
         B = clean.shape[0]
         acc = None
         for i in range(num_samples):
