@@ -275,7 +275,7 @@ class ConceptAttentionFluxPipeline:
                                    "latents [B,16,h/8,w/8] instead")
             # uint8 HWC goes to the device as it is; scale, resize (nearest, as torch's
             # F.interpolate default in segmentation.py:115-131) and VAE encode run there
-            arr = torch.from_numpy(np.asarray(image.convert("RGB"))).to(dev, non_blocking=True)
+            arr = torch.from_numpy(np.array(image.convert("RGB"))).to(dev, non_blocking=True)
             arr = arr.permute(2, 0, 1).float() / 255.0
             arr = torch.nn.functional.interpolate((2.0 * arr - 1.0)[None], (height, width))
             with torch.autocast(device_type=dev.type, dtype=torch.bfloat16):
