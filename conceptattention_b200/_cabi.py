@@ -50,6 +50,8 @@ SIGNATURES = {
     "ca_seq_unpack_qkv": [_p, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p],
     "ca_seq_pack_out": [_p, _p, _i, _i, _i, _i, _i, _p, _p],
     "ca_seq_unpack_out": [_p, _i, _i, _i, _i, _i, _p, _p, _p],
+    "ca_seq_gather_qkv": [_p, C.c_int64, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p],
+    "ca_seq_gather_out": [_p, C.c_int64, C.c_int64, _i, _i, _i, _i, _i, _i, _p, _p, _p],
     "ca_heatmaps_from_vectors_host": [_p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _i, _i, _p],
 }
 _RESTYPES = {"ca_version": C.c_char_p, "ca_status_string": C.c_char_p,

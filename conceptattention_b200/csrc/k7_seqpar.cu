@@ -74,6 +74,61 @@ seq_unpack_out_kernel(const uint4* __restrict__ recv, int W, int Hl, int Pl, int
   dst[(int64_t)w * rv + c] = __ldg(recv + i);
 }
 
+// ---- fused exchange: pull straight out of the peers' buffers over NVLink ---------------------------
+// peers[w] = base of rank w's symmetric allocation as mapped into THIS process (P2P / fabric
+// handles, exchanged once by the host side); every rank uses the same byte offsets inside it.
+// Same permutation as seq_unpack_qkv with recv[w] := (rank w's send buffer)[self]: the all-to-all
+// and its staging buffer disappear, the loads below ARE the exchange.
+__global__ void __launch_bounds__(256)
+seq_gather_qkv_kernel(const uint8_t* const* __restrict__ peers, int64_t send_off, int W, int self, int Hl,
+                      int Pl, int Tl, int C, uint4* __restrict__ q, uint4* __restrict__ k,
+                      uint4* __restrict__ v) {
+  const int Nl = Pl + Tl + C;
+  const int64_t N = (int64_t)W * (Pl + Tl) + C;
+  const int64_t chunk = (int64_t)3 * Hl * Nl * 16;          // 16-byte vectors per destination chunk
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= chunk * W) return;
+  const int w = (int)(i / chunk);
+  const int64_t j = i - (int64_t)w * chunk;                 // offset inside the chunk
+  const int c16 = (int)(j & 15);
+  int64_t r = j >> 4;
+  const int row = (int)(r % Nl); r /= Nl;
+  const int hl = (int)(r % Hl);
+  const int t = (int)(r / Hl);
+  int64_t dst_row;
+  if (row < Pl) dst_row = (int64_t)w * Pl + row;
+  else if (row < Pl + Tl) dst_row = (int64_t)W * Pl + (int64_t)w * Tl + (row - Pl);
+  else if (w == self) dst_row = (int64_t)W * (Pl + Tl) + (row - Pl - Tl);
+  else return;
+  const uint4* src = reinterpret_cast<const uint4*>(peers[w] + send_off) + (int64_t)self * chunk + j;
+  uint4* dst = t == 0 ? q : (t == 1 ? k : v);
+  dst[((int64_t)hl * N + dst_row) * 16 + c16] = *src;
+}
+
+// attn_img [Pl][W*Hl*128], attn_tc [Tl+C][W*Hl*128] <- rows of THIS rank out of every peer's K2
+// outputs out_img [W*Pl][Hl*128] (at img_off) and out_txtc [W*Tl+C][Hl*128] (at tc_off): what
+// seq_pack_out + all-to-all + seq_unpack_out did in three passes.
+__global__ void __launch_bounds__(256)
+seq_gather_out_kernel(const uint8_t* const* __restrict__ peers, int64_t img_off, int64_t tc_off, int W,
+                      int self, int Hl, int Pl, int Tl, int C, uint4* __restrict__ attn_img,
+                      uint4* __restrict__ attn_tc) {
+  const int Nl = Pl + Tl + C, rv = Hl * 16;
+  const int64_t total = (int64_t)W * Nl * rv;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = (int)(i % rv);
+  int64_t r = i / rv;
+  const int row = (int)(r % Nl);
+  const int w = (int)(r / Nl);
+  const uint4* src;
+  if (row < Pl) src = reinterpret_cast<const uint4*>(peers[w] + img_off) + ((int64_t)self * Pl + row) * rv;
+  else if (row < Pl + Tl)
+    src = reinterpret_cast<const uint4*>(peers[w] + tc_off) + ((int64_t)self * Tl + (row - Pl)) * rv;
+  else src = reinterpret_cast<const uint4*>(peers[w] + tc_off) + ((int64_t)W * Tl + (row - Pl - Tl)) * rv;
+  uint4* dst = row < Pl ? attn_img + (int64_t)row * W * rv : attn_tc + (int64_t)(row - Pl) * W * rv;
+  dst[(int64_t)w * rv + c] = src[c];
+}
+
 static bool seq_args_ok(int W, int Hl, int Pl, int Tl, int C) {
   return W > 0 && Hl > 0 && Pl >= 0 && Tl >= 0 && C >= 0;
 }
@@ -127,6 +182,46 @@ extern "C" ca_status ca_seq_unpack_out(const void* recv, int W, int Hl, int Pl, 
   if (blocks > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
   seq_unpack_out_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
       (const uint4*)recv, W, Hl, Pl, Tl, C, (uint4*)attn_img, (uint4*)attn_tc);
+  CA_LAUNCH_CHECK();
+  return CA_OK;
+}
+
+extern "C" ca_status ca_seq_gather_qkv(const void* const* peers_dev, int64_t send_off, int W, int self,
+                                       int Hl, int Pl, int Tl, int C, void* q, void* k, void* v,
+                                       void* stream) {
+  using namespace ca;
+  if (!seq_args_ok(W, Hl, Pl, Tl, C) || self < 0 || self >= W || !peers_dev || !q || !k || !v || send_off < 0)
+    return CA_ERR_INVALID_ARG;
+  const void* ptrs[] = {q, k, v};
+  for (const void* p : ptrs) if (!aligned16(p)) return CA_ERR_ALIGNMENT;
+  if (send_off % 16) return CA_ERR_ALIGNMENT;
+  const int64_t total = (int64_t)W * 3 * Hl * (Pl + Tl + C) * 16;
+  if (total == 0) return CA_OK;
+  const int64_t blocks = (total + 255) / 256;
+  if (blocks > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
+  seq_gather_qkv_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      (const uint8_t* const*)peers_dev, send_off, W, self, Hl, Pl, Tl, C, (uint4*)q, (uint4*)k, (uint4*)v);
+  CA_LAUNCH_CHECK();
+  return CA_OK;
+}
+
+extern "C" ca_status ca_seq_gather_out(const void* const* peers_dev, int64_t img_off, int64_t tc_off, int W,
+                                       int self, int Hl, int Pl, int Tl, int C, void* attn_img,
+                                       void* attn_tc, void* stream) {
+  using namespace ca;
+  if (!seq_args_ok(W, Hl, Pl, Tl, C) || self < 0 || self >= W || !peers_dev || img_off < 0 || tc_off < 0 ||
+      (Pl > 0 && !attn_img) || (Tl + C > 0 && !attn_tc))
+    return CA_ERR_INVALID_ARG;
+  const void* ptrs[] = {attn_img, attn_tc};
+  for (const void* p : ptrs) if (p && !aligned16(p)) return CA_ERR_ALIGNMENT;
+  if (img_off % 16 || tc_off % 16) return CA_ERR_ALIGNMENT;
+  const int64_t total = (int64_t)W * (Pl + Tl + C) * Hl * 16;
+  if (total == 0) return CA_OK;
+  const int64_t blocks = (total + 255) / 256;
+  if (blocks > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
+  seq_gather_out_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      (const uint8_t* const*)peers_dev, img_off, tc_off, W, self, Hl, Pl, Tl, C, (uint4*)attn_img,
+      (uint4*)attn_tc);
   CA_LAUNCH_CHECK();
   return CA_OK;
 }

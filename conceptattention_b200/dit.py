@@ -328,6 +328,29 @@ class FluxDiTEngine:
             self._rope_cache.update(key=key, ids=parts, table=tables[digest])
         return self._rope_cache["table"]
 
+    def _peer_regions(self, Pl, Tl, C, dev):
+        """Symmetric-memory regions of the fused sequence-parallel exchange (None: NCCL path):
+        send [W,3,Hl,Pl+Tl+C,128] | K2 out_img [W*Pl,Hl*128] | K2 out_txtc [W*Tl+C,Hl*128], bf16,
+        sized for the double blocks (single blocks use the same offsets with C = 0)."""
+        hs = self.hs
+        W, Hl = hs.world, hs.h_local
+        al = lambda n: (n + 1023) // 1024 * 1024
+        send_b = al(W * 3 * Hl * (Pl + Tl + C) * 256)
+        img_b = al(W * Pl * Hl * 256)
+        tc_b = al((W * Tl + C) * Hl * 256)
+        sym = hs.symmetric_workspace(send_b + img_b + tc_b, dev)
+        if sym is None:
+            return None
+        buf, hdl = sym
+
+        def view(off, shape):
+            n = 2
+            for d in shape:
+                n *= d
+            return buf[off:off + n].view(torch.bfloat16).view(shape)
+        return {"hdl": hdl, "ptrs": hdl.buffer_ptrs_dev, "view": view,
+                "send_off": 0, "img_off": send_b, "tc_off": send_b + img_b}
+
     def _rope_local(self, rope, P, T):
         """Sequence-parallel mode: this rank's rows [img_l | txt_l | concept] of the full table
         (rows [img P | txt T | concept]).  One table per (full table, P, T), kept beside the full
@@ -459,6 +482,7 @@ class FluxDiTEngine:
             Pg, Tg, P, T = P, T, P // W, T // W
             img, txt = img[:, rk * P:(rk + 1) * P], txt[:, rk * T:(rk + 1) * T]
             rope = self._rope_local(rope, Pg, Tg)            # rows [img_l | txt_l | concept]
+        peer = self._peer_regions(P, T, C, dev) if seqpar else None
         x_img = self._lin("img_in", img).contiguous()
         vec, cvec = cond(y), cond(concept_vec)
         txtc = self._lin("txt_in", torch.cat((txt, concepts), 1)).contiguous()   # [B,T+C,D]
@@ -518,6 +542,27 @@ class FluxDiTEngine:
                 o = (None, None) if out is None else out
                 a_img, a_tc = ops.joint_attention(res[0], res[1], res[2], P, T, n_con, amode, o[0], o[1])
                 return a_img, a_tc, (res[3] if want_q_pre else None)
+            if peer is not None:
+                # fused exchange over peer memory: K1b writes this rank's send region, ONE cross-GPU
+                # barrier, then the gather kernel pulls the q/k/v of this rank's heads out of every
+                # peer; K2 writes its outputs into the symmetric region, one barrier, and the
+                # second gather pulls this rank's rows of every peer's heads.  A region is written
+                # again only after the NEXT barrier, which a peer reaches after its reads.
+                Hl, Nl = self.hs.h_local, P + T + n_con
+                send = peer["view"](peer["send_off"], (W, 3, Hl, Nl, 128))
+                o_img = peer["view"](peer["img_off"], (1, W * P, Hl * 128))
+                o_tc = peer["view"](peer["tc_off"], (1, W * T + n_con, Hl * 128))
+                _, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H, Hl,
+                                                want_q_pre=want_q_pre, send=send)
+                if meanwhile is not None:
+                    meanwhile()
+                peer["hdl"].barrier(channel=0)
+                q, k, v = ops.seq_gather_qkv(peer["ptrs"], peer["send_off"], W, rk, Hl, P, T, n_con, dev)
+                ops.joint_attention(q, k, v, Pg, Tg, n_con, amode, o_img, o_tc)
+                peer["hdl"].barrier(channel=0)
+                a_img, a_tc = ops.seq_gather_out(peer["ptrs"], peer["img_off"], peer["tc_off"], W, rk, Hl,
+                                                 P, T, n_con, dev, out)
+                return a_img, a_tc, q_pre
             send, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H,
                                                self.hs.h_local, want_q_pre=want_q_pre)
             recv, wait = self.hs.all_to_all_begin(send)

@@ -141,7 +141,7 @@ def qkv_prep(qkv_a, qkv_b, scales_a, scales_b, rope, H, want_q_pre=False):
     return (q, k, v, q_pre) if want_q_pre else (q, k, v)
 
 
-def qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope, H, G, want_q_pre=False):
+def qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope, H, G, want_q_pre=False, send=None):
     """K1b for the sequence-parallel exchange (B = 1): same maths as `qkv_prep`, q/k/v written as
     one send buffer [H/G, 3, G, N, 128] (chunk w = the q, k, v of rank w's G heads over this rank's
     N rows).  Returns (send, q_pre | None); q_pre keeps [1, H, N, 128]."""
@@ -154,7 +154,11 @@ def qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope, H, G, want_q_pre=Fa
     _req(rope, torch.float32, "rope")
     assert rope.shape == (Na + Nb, 64, 2), rope.shape
     N = Na + Nb
-    send = torch.empty(H // G, 3, G, N, 128, device=qkv_a.device, dtype=BF16)
+    if send is None:
+        send = torch.empty(H // G, 3, G, N, 128, device=qkv_a.device, dtype=BF16)
+    else:                                   # caller-owned (e.g. a symmetric-memory region)
+        _req(send, BF16, "send")
+        assert send.shape == (H // G, 3, G, N, 128) and send.is_contiguous()
     q_pre = torch.empty(1, H, N, 128, device=qkv_a.device, dtype=BF16) if want_q_pre else None
     sb = scales_b if scales_b is not None else (None, None)
     slab = G * N * 128 * 2                                     # bytes of one [G,N,128] slab
@@ -182,6 +186,32 @@ def seq_unpack_qkv(recv, self_rank, Pl, Tl, C):
     check(_cabi.load().ca_seq_unpack_qkv(recv.data_ptr(), W, self_rank, Hl, Pl, Tl, C, q.data_ptr(),
                                          k.data_ptr(), v.data_ptr(), _stream(recv)), "ca_seq_unpack_qkv")
     return q, k, v
+
+
+def seq_gather_qkv(peers_dev, send_off, W, self_rank, Hl, Pl, Tl, C, device):
+    """Fused exchange: q,k,v [1,Hl,W*(Pl+Tl)+C,128] pulled out of the peers' send buffers
+    (`peers_dev`: device array of W base pointers, `send_off`: byte offset of the send region)."""
+    N = W * (Pl + Tl) + C
+    q, k, v = (torch.empty(1, Hl, N, 128, device=device, dtype=BF16) for _ in range(3))
+    check(_cabi.load().ca_seq_gather_qkv(peers_dev, send_off, W, self_rank, Hl, Pl, Tl, C, q.data_ptr(),
+                                         k.data_ptr(), v.data_ptr(),
+                                         torch.cuda.current_stream(device).cuda_stream), "ca_seq_gather_qkv")
+    return q, k, v
+
+
+def seq_gather_out(peers_dev, img_off, tc_off, W, self_rank, Hl, Pl, Tl, C, device, out=None):
+    """Fused return exchange: this rank's rows with all heads, attn_img [1,Pl,W*Hl*128] and attn_tc
+    [1,Tl+C,W*Hl*128], pulled out of every peer's K2 outputs."""
+    K = W * Hl * 128
+    if out is None:
+        attn_img = torch.empty(1, Pl, K, device=device, dtype=BF16)
+        attn_tc = torch.empty(1, Tl + C, K, device=device, dtype=BF16)
+    else:
+        attn_img, attn_tc = out
+    check(_cabi.load().ca_seq_gather_out(peers_dev, img_off, tc_off, W, self_rank, Hl, Pl, Tl, C,
+                                         attn_img.data_ptr(), attn_tc.data_ptr(),
+                                         torch.cuda.current_stream(device).cuda_stream), "ca_seq_gather_out")
+    return attn_img, attn_tc
 
 
 def seq_pack_out(out_img, out_txtc, W, Pl, Tl, C):

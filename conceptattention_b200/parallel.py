@@ -95,8 +95,12 @@ class HeadShard:
     # REPLICATED weights, heads split only inside the attention (two all-to-alls per block instead
     # of an all-reduce after every row-parallel linear).  B = 1, rows divisible by world.
     sequence_parallel: bool = False
+    # sequence-parallel exchanges through peer memory instead of NCCL all-to-all: None = use it
+    # when torch's symmetric memory can be set up on this group (NCCL, CUDA), False = never
+    peer_exchange: object = None
 
     def __post_init__(self):
+        self._symm = None
         if self.num_heads % self.world:
             raise ValueError(f"{self.num_heads} heads do not split over {self.world} ranks")
         self.h_local = self.num_heads // self.world
@@ -155,6 +159,38 @@ class HeadShard:
             row_parallel(pre + ".linear2a", hcols, bias_key=pre + ".linear2.bias")
             sd[pre + ".linear2b.weight"] = sd[pre + ".linear2b.weight"][:, mcols].contiguous()
         return sd
+
+    # -- peer memory ------------------------------------------------------------------
+    def symmetric_workspace(self, nbytes: int, device):
+        """One symmetric allocation of >= nbytes on every rank of the group, mapped into every
+        peer (torch.distributed._symmetric_memory: CUDA VMM handles exchanged at rendezvous).
+        Returns (uint8 tensor, handle) — handle.buffer_ptrs_dev is the device array of the W peer
+        base pointers, handle.barrier() a cross-GPU barrier kernel on the current stream — or
+        None when peer exchange is off / unavailable (gloo, one rank).  COLLECTIVE: every rank
+        must call it with the same size at the same point."""
+        if self.peer_exchange is False or self.world == 1 or self._gloo():
+            return None
+        if self._symm is not None and self._symm[0].numel() >= nbytes:
+            return self._symm
+        try:
+            import torch.distributed._symmetric_memory as symm
+            grp = self.group if self.group is not None else dist.group.WORLD
+            buf = symm.empty(int(nbytes), dtype=torch.uint8, device=device)
+            hdl = symm.rendezvous(buf, grp)
+            ok = torch.ones(1, device=device)
+        except Exception as e:                                  # noqa: BLE001
+            if self.peer_exchange is True:
+                raise
+            import warnings
+            warnings.warn(f"peer exchange unavailable ({type(e).__name__}: {e}); using NCCL all-to-all")
+            buf = hdl = None
+            ok = torch.zeros(1, device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)   # all ranks or none
+        if ok.item() < 1:
+            self.peer_exchange = False
+            return None
+        self._symm = (buf, hdl)
+        return self._symm
 
     # -- collectives ------------------------------------------------------------------
     def _gloo(self) -> bool:

@@ -246,6 +246,24 @@ ca_status ca_seq_pack_out(const void* out_img, const void* out_txtc, int W, int 
 ca_status ca_seq_unpack_out(const void* recv, int W, int Hl, int Pl, int Tl, int C,
                             void* attn_img, void* attn_tc, void* stream);
 
+/* Fused form of the two exchanges: the kernels PULL their input straight out of the peers' buffers
+ * over NVLink instead of unpacking what a collective delivered.  `peers_dev` is a DEVICE array of W
+ * pointers, entry w = base of rank w's symmetric allocation as mapped into this process (CUDA VMM /
+ * IPC handles exchanged once by the host side; torch.distributed._symmetric_memory provides both
+ * the mapping and the cross-GPU barrier); all ranks use the same byte offsets inside it.
+ *   ca_seq_gather_qkv  == ca_seq_unpack_qkv with recv[w] := (rank w's send [W][3][Hl][Nl][128] at
+ *                      send_off)[self]: replaces all-to-all + unpack
+ *   ca_seq_gather_out  attn_img / attn_tc of this rank's rows from every peer's K2 outputs out_img
+ *                      [W*Pl][Hl*128] (img_off) and out_txtc [W*Tl+C][Hl*128] (tc_off): replaces
+ *                      ca_seq_pack_out + all-to-all + ca_seq_unpack_out
+ * The caller orders the ranks: a barrier between the writes of the buffers and these reads; the next
+ * write of a buffer happens after the NEXT barrier, which every peer reaches only after its reads. */
+ca_status ca_seq_gather_qkv(const void* const* peers_dev, int64_t send_off, int W, int self, int Hl,
+                            int Pl, int Tl, int C, void* q, void* k, void* v, void* stream);
+ca_status ca_seq_gather_out(const void* const* peers_dev, int64_t img_off, int64_t tc_off, int W,
+                            int self, int Hl, int Pl, int Tl, int C, void* attn_img, void* attn_tc,
+                            void* stream);
+
 /* ---- host-buffer form of compute_heatmaps_from_vectors (:29-91) --------------
  * image_host  bf16 [Nt,L,B,P,K]   (or per-head [Nt,L,B,H,P,d] when per_head != 0)
  * concept_host bf16 [Nt,L,B,C,K]  (or [Nt,L,B,H,C,d])

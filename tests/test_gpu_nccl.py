@@ -47,10 +47,14 @@ def _worker(rank, world, port, ret):
         return pred.float().cpu(), out.cpu().clone(), cross.cpu().clone()
 
     res = {"full": run(FluxDiTEngine(p, sd, dev))}
-    for mode in ("sequence", "tensor"):
-        eng = FluxDiTEngine(p, sd, dev, head_shard=HeadShard(rank, world, p.num_heads,
-                                                             sequence_parallel=mode == "sequence"))
+    for mode in ("sequence", "sequence_nccl", "tensor"):
+        # "sequence": exchanges through peer memory (symmetric allocation + barrier + gather kernels)
+        # when torch can set it up, "sequence_nccl": the NCCL all-to-all form of the same exchange
+        eng = FluxDiTEngine(p, sd, dev, head_shard=HeadShard(
+            rank, world, p.num_heads, sequence_parallel=mode.startswith("sequence"),
+            peer_exchange=False if mode == "sequence_nccl" else None))
         res[mode + "_eager"] = run(eng)
+        res[mode + "_peer"] = eng.hs._symm is not None
         run(eng)                                           # second sighting: capture
         res[mode + "_replay"] = run(eng)
         res[mode + "_graphs"] = len(eng._graphs)
@@ -82,14 +86,16 @@ def test_head_sharded_modes_over_nccl_on_two_gpus():
     full, ora = ret["full"], ret["oracle"]
     rel = lambda a, b: ((a - b).abs().max() / b.abs().max()).item()
     mae = lambda a, b: (a - b).abs().mean().item()
-    for mode in ("sequence", "tensor"):
+    print("peer-memory exchange active:", ret["sequence_peer"])
+    assert not ret["sequence_nccl_peer"]
+    for mode in ("sequence", "sequence_nccl", "tensor"):
         eager, replay = ret[mode + "_eager"], ret[mode + "_replay"]
         assert ret[mode + "_graphs"] >= 1, mode
         for a, b in zip(eager, replay):
             assert torch.equal(a, b), mode                # graph replay == eager, bit for bit
         d = [rel(a, b) for a, b in zip(eager, full)]
         print(f"NCCL 2 GPUs [{mode}-parallel] vs one-GPU engine: pred {d[0]:.3e} output {d[1]:.3e} cross {d[2]:.3e}")
-        if mode == "sequence":
+        if mode.startswith("sequence"):
             assert torch.equal(eager[0], full[0])          # same rows, same GEMMs, elsewhere
             assert d[1] < 1e-5 and d[2] < 1e-5
         else:
