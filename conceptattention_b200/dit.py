@@ -548,19 +548,19 @@ class FluxDiTEngine:
                 # peer; K2 writes its outputs into the symmetric region, one barrier, and the
                 # second gather pulls this rank's rows of every peer's heads.  A region is written
                 # again only after the NEXT barrier, which a peer reaches after its reads.
-                Hl, Nl = self.hs.h_local, P + T + n_con
-                send = peer["view"](peer["send_off"], (W, 3, Hl, Nl, 128))
-                o_img = peer["view"](peer["img_off"], (1, W * P, Hl * 128))
-                o_tc = peer["view"](peer["tc_off"], (1, W * T + n_con, Hl * 128))
-                _, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H, Hl,
+                hloc, nloc = self.hs.h_local, P + T + n_con
+                send = peer["view"](peer["send_off"], (W, 3, hloc, nloc, 128))
+                o_img = peer["view"](peer["img_off"], (1, W * P, hloc * 128))
+                o_tc = peer["view"](peer["tc_off"], (1, W * T + n_con, hloc * 128))
+                _, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H, hloc,
                                                 want_q_pre=want_q_pre, send=send)
                 if meanwhile is not None:
                     meanwhile()
                 peer["hdl"].barrier(channel=0)
-                q, k, v = ops.seq_gather_qkv(peer["ptrs"], peer["send_off"], W, rk, Hl, P, T, n_con, dev)
+                q, k, v = ops.seq_gather_qkv(peer["ptrs"], peer["send_off"], W, rk, hloc, P, T, n_con, dev)
                 ops.joint_attention(q, k, v, Pg, Tg, n_con, amode, o_img, o_tc)
                 peer["hdl"].barrier(channel=0)
-                a_img, a_tc = ops.seq_gather_out(peer["ptrs"], peer["img_off"], peer["tc_off"], W, rk, Hl,
+                a_img, a_tc = ops.seq_gather_out(peer["ptrs"], peer["img_off"], peer["tc_off"], W, rk, hloc,
                                                  P, T, n_con, dev, out)
                 return a_img, a_tc, q_pre
             send, q_pre = ops.qkv_prep_grouped(qkv_a, qkv_b, scales_a, scales_b, rope_x, H,
