@@ -144,7 +144,8 @@ def run_ours(args, rank, world, local_rank, secondary=False):
     if sharded:
         from conceptattention_b200.weights import CONFIGS
         hs = HeadShard(rank, world, CONFIGS[wl["model"]].num_heads,
-                       sequence_parallel=args.hs_mode == "sequence")
+                       sequence_parallel=args.hs_mode == "sequence",
+                       peer_exchange=False if getattr(args, "no_peer_exchange", False) else None)
     from conceptattention_b200.weights import CONFIGS, init_state_dict
     # random-init weights with the reference's keys, drawn on the device; the same tensors are
     # handed to the reference modules of the gpu_reference arm (shared storage)
@@ -571,6 +572,8 @@ def main():
                          "2 GPUs (measured: 4.22 vs 3.19 images/s on 8, 1.22 vs 1.27 on 2)")
     ap.add_argument("--tp-overlap", action="store_true",
                     help="head-sharded mode: two token chunks on two streams around the all-reduces (A/B)")
+    ap.add_argument("--no-peer-exchange", action="store_true",
+                    help="sequence-parallel exchanges through NCCL all-to-all instead of peer memory (A/B)")
     ap.add_argument("--no-side-stream", action="store_true", help="text stream on the main CUDA stream (A/B)")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip the reference-on-the-same-GPU arm")
     ap.add_argument("--no-other-configs", action="store_true", help="skip the short runs of the other configs")
