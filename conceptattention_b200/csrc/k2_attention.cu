@@ -40,8 +40,7 @@ struct AttnParams {
   // flat 1-D grid: [ concept units | whole main units | stream-K tail pieces ] — the concept units
   // (one 128-row tile over all P+C keys: long and not splittable here) start first, the short tail
   // pieces fill the SMs last
-  int n_pairs;                         // main units per (b,h): ceil(n_main_tiles / tiles_per_unit)
-  int tiles_per_unit;                  // 2 = a pair of query tiles per CTA (default), 1 = one tile
+  int n_pairs;                         // main units (query-tile pairs) per (b,h)
   int n_dp;                            // main units run whole, one CTA each
   int sk_units;                        // tail main units whose key steps are spread over sk_sms ranges
   int sk_sms;                          // number of ranges (2 CTAs per range, possibly empty); 0 = no split
@@ -178,10 +177,10 @@ __device__ __forceinline__ UnitV1 decode_unit(const AttnParams& p, int cta) {
     }
     u.bh = unit / p.n_pairs;
     const int pair = unit - u.bh * p.n_pairs;
-    u.n_q = min(p.tiles_per_unit, p.n_main_tiles - p.tiles_per_unit * pair);
+    u.n_q = min(2, p.n_main_tiles - 2 * pair);
 #pragma unroll
     for (int t = 0; t < 2; ++t) {
-      u.q_row0[t] = (p.tiles_per_unit * pair + t) * kBM;
+      u.q_row0[t] = (2 * pair + t) * kBM;
       u.q_rows[t] = max(0, min(kBM, PT - u.q_row0[t]));
     }
   }
@@ -679,17 +678,6 @@ static SkPlan plan_streamk_core(int W, int n_concept, int n_steps, int S, bool a
   return pl;
 }
 
-static int sm_count_cached() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-      n = 0;
-  }
-  return n;
-}
-
 }  // namespace ca
 
 
@@ -771,7 +759,6 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   p.out_img = (__nv_bfloat16*)out_img;
   p.out_txtc = (__nv_bfloat16*)out_txtc;
   p.scale_log2 = kLog2e / sqrtf((float)kD);
-  p.tiles_per_unit = 2;
   p.n_pairs = (p.n_main_tiles + 1) / 2;
   p.ws_part = nullptr; p.ws_count = nullptr;
 
@@ -783,22 +770,8 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
 
   const bool concept_attn = C > 0 && mode != CA_ATTN_NEITHER;
   const int kernel = resolve_impl(impl, p.n_main_tiles);
-  p.n_concept = concept_attn ? B * H : 0;
-  if (kernel != CA_K2_V3) {
-    // One query tile per CTA instead of two when that fills the waves better.  A one-tile CTA
-    // runs at the same cost PER TILE (the pair is softmax-bound: its two warpgroups take as long
-    // side by side as one does alone), so only the rounding to whole waves differs: time ~
-    // ceil(units / SMs) * tiles per unit.  Config 5 on 8 GPUs: 201 two-tile units = 2 waves of 148
-    // SMs, 393 one-tile units = 3 half-waves (measured 0.44 -> see profiles/r02_k2_variants.md).
-    const int sms = sm_count_cached();
-    if (sms > 0) {
-      const int64_t w2 = (int64_t)p.n_pairs * B * H + p.n_concept;
-      const int64_t w1 = (int64_t)p.n_main_tiles * B * H + p.n_concept;
-      const int64_t t2 = 2 * ((w2 + sms - 1) / sms), t1 = (w1 + sms - 1) / sms;
-      if (t1 * 10 <= t2 * 9) { p.tiles_per_unit = 1; p.n_pairs = p.n_main_tiles; }
-    }
-  }
   const int W = p.n_pairs * B * H;
+  p.n_concept = concept_attn ? B * H : 0;
   const size_t need = ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, impl, plan_sms);
   const SkPlan pl = plan_streamk(W, p.n_concept, p.n_main_tiles,
                                  kernel == CA_K2_V3 && workspace != nullptr && need > 0 && workspace_bytes >= need,
