@@ -31,25 +31,37 @@ struct SmemV7 {
   uint32_t tmem_base;
 };
 
+// The first loads of a CTA (Q0, K0, Q1) are issued by thread 0 right after it has initialised the
+// barriers, BEFORE the TMEM allocation and the CTA-wide sync: their ~1 us round trip then runs
+// under the rest of the prologue instead of after it (kHead = true); the producer warp carries on
+// from ring item 1 (kHead = false).
+template <typename Smem, int kStages>
+__device__ __forceinline__ void k2_load_tile(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0, int bh) {
+  mbar_expect_tx(bar, kTileBytes);
+  tma_load_3d(dst, tm, bar, 0, row0, bh);
+  tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
+}
+
+template <typename Smem, int kStages>
+__device__ __forceinline__ void k2_first_loads(Smem& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
+                                               const UnitV1& u, int bh) {
+  int row0, valid; key_tile(u.ks, u.n0, u.j_begin, row0, valid);
+  k2_load_tile<Smem, kStages>(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0], bh);
+  k2_load_tile<Smem, kStages>(sm.kv[0], tmk, &sm.kv_full[0], row0, bh);          // ring item 0, slot 0: free at start
+  if (u.n_q == 2) k2_load_tile<Smem, kStages>(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1], bh);
+}
+
 __device__ __forceinline__ void v7_producer(SmemV7& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
                                             const CUtensorMap* tmv, const UnitV1& u, int bh) {
-  int item = 0;
-  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
-    mbar_expect_tx(bar, kTileBytes);
-    tma_load_3d(dst, tm, bar, 0, row0, bh);
-    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
-  };
+  int item = 1;                                            // item 0 (K0) and the Q tiles: k2_first_loads
   auto load_kv = [&](const CUtensorMap* tm, int j) {
     int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
     const int slot = item % kV7Stages;
     mbar_wait(&sm.kv_empty[slot], ((item / kV7Stages) & 1) ^ 1);
-    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    k2_load_tile<SmemV7, kV7Stages>(sm.kv[slot], tm, &sm.kv_full[slot], row0, bh);
     ++item;
   };
   const int n = u.n_local;
-  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
-  load_kv(tmk, 0);
-  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
   if (n > 1) load_kv(tmk, 1);
   for (int j = 0; j < n; ++j) {
     load_kv(tmv, j);
@@ -281,6 +293,7 @@ attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
     }
     mbar_init(&sm.o_done, 1);
     fence_barrier_init();
+    k2_first_loads<SmemV7, kV7Stages>(sm, &tmq, &tmk, u, bh);
   }
   if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
   tc_fence_before();
@@ -329,23 +342,15 @@ struct SmemV11 {
 
 __device__ __forceinline__ void v11_producer(SmemV11& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
                                              const CUtensorMap* tmv, const UnitV1& u, int bh) {
-  int item = 0;
-  auto load_tile = [&](uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0) {
-    mbar_expect_tx(bar, kTileBytes);
-    tma_load_3d(dst, tm, bar, 0, row0, bh);
-    tma_load_3d(dst + kHalfBytes, tm, bar, 64, row0, bh);
-  };
+  int item = 1;                                            // item 0 (K0) and the Q tiles: k2_first_loads
   auto load_kv = [&](const CUtensorMap* tm, int j) {
     int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
     const int slot = item % kV11Stages;
     mbar_wait(&sm.kv_empty[slot], ((item / kV11Stages) & 1) ^ 1);
-    load_tile(sm.kv[slot], tm, &sm.kv_full[slot], row0);
+    k2_load_tile<SmemV11, kV11Stages>(sm.kv[slot], tm, &sm.kv_full[slot], row0, bh);
     ++item;
   };
   const int n = u.n_local;
-  load_tile(sm.q[0], tmq, &sm.q_full[0], u.q_row0[0]);
-  load_kv(tmk, 0);
-  if (u.n_q == 2) load_tile(sm.q[1], tmq, &sm.q_full[1], u.q_row0[1]);
   for (int j = 0; j < n; ++j) {
     if (j + 1 < n) load_kv(tmk, j + 1);
     load_kv(tmv, j);
@@ -561,6 +566,7 @@ attn_v11_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__
     mbar_init(&sm.s_free, 4);
     mbar_init(&sm.o_done, 1);
     fence_barrier_init();
+    k2_first_loads<SmemV11, kV11Stages>(sm, &tmq, &tmk, u, bh);
   }
   if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
   tc_fence_before();
