@@ -15,7 +15,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libconcept
 CA_OK = 0
 NORM = {"softmax": 0, "sparsemax": 1, "entmax15": 2, "none": 3}
 ATTN_BOTH, ATTN_CROSS_ONLY, ATTN_SELF_ONLY, ATTN_NEITHER = 0, 1, 2, 3
-K2_AUTO, K2_V3, K2_V7, K2_V11 = 0, 1, 2, 3
+K2_AUTO, K2_V3, K2_V7, K2_V11, K2_V11P = 0, 1, 2, 3, 4
 MAX_CONCEPTS = 32            # CA_MAX_CONCEPTS
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float

@@ -743,7 +743,7 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   using namespace ca;
   if (!q || !k || !v || B < 0 || H <= 0 || P < 0 || T < 0 || C < 0) return CA_ERR_INVALID_ARG;
   if (mode < CA_ATTN_BOTH || mode > CA_ATTN_NEITHER) return CA_ERR_INVALID_ARG;
-  if (impl < CA_K2_AUTO || impl > CA_K2_V11) return CA_ERR_INVALID_ARG;
+  if (impl < CA_K2_AUTO || impl > CA_K2_V11P) return CA_ERR_INVALID_ARG;
   if (C > CA_MAX_CONCEPTS) return CA_ERR_UNSUPPORTED;
   if ((P > 0 && !out_img) || (T + C > 0 && !out_txtc)) return CA_ERR_INVALID_ARG;
   const void* ptrs[] = {q, k, v, out_img, out_txtc, workspace};
@@ -786,7 +786,21 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   if (ctas > 0x7fffffffLL) return CA_ERR_UNSUPPORTED;
   if (ctas > 0) {
     // every kernel: polynomial exp2 on every 4th element pair (the MUFU / FMA-pipe balance point)
-    if (kernel == CA_K2_V11) s = launch_k2<attn_v11_kernel<4>>((int)sizeof(SmemV11) + 1024, ctas, st, tmq, tmk, tmv, p);
+    if (kernel == CA_K2_V11P) {
+      static bool configured = false;
+      static int sms = 0;
+      const int smem = (int)sizeof(SmemV11) + 1024;
+      if (!configured) {
+        int dev = 0;
+        CA_CUDA_OK(cudaGetDevice(&dev));
+        CA_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        CA_CUDA_OK(cudaFuncSetAttribute(attn_v11p_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured = true;
+      }
+      attn_v11p_kernel<4><<<(unsigned)(ctas < sms ? ctas : sms), 384, smem, st>>>(tmq, tmk, tmv, p, (int)ctas);
+      CA_LAUNCH_CHECK();
+      s = CA_OK;
+    } else if (kernel == CA_K2_V11) s = launch_k2<attn_v11_kernel<4>>((int)sizeof(SmemV11) + 1024, ctas, st, tmq, tmk, tmv, p);
     else if (kernel == CA_K2_V7) s = launch_k2<attn_v7_kernel<4>>((int)sizeof(SmemV7) + 1024, ctas, st, tmq, tmk, tmv, p);
     else s = launch_k2<attn_v3_kernel<4>>((int)sizeof(SmemV1) + 1024, ctas, st, tmq, tmk, tmv, p);
     if (s != CA_OK) return s;

@@ -337,27 +337,52 @@ struct SmemV11 {
   uint8_t kv[kV11Stages][kTileBytes];
   uint64_t q_full[2], kv_full[kV11Stages], kv_empty[kV11Stages];
   uint64_t s_full[2], s_free, p_full[2][2], pv_done[2], o_done;
+  uint64_t q_empty[2];                                      // persistent form only
   uint32_t tmem_base;
 };
 
+// Phase counters that run on from unit to unit in the persistent form (all zero for a
+// one-unit CTA): every mbarrier wait below takes its parity from them.
+struct V11Carry {
+  int item = 0;        // K/V ring items so far (producer and MMA thread each keep their own copy)
+  int n_qk = 0;        // score tiles issued so far: the k-th waits for phase k-1 of s_free
+  int steps[2] = {0, 0};   // key steps so far per tile: s_full / p_full / pv_done phases
+  int units[2] = {0, 0};   // units so far that used tile t: q_full / q_empty phases
+  int n_units = 0;     // units so far: o_done phases
+};
+
 __device__ __forceinline__ void v11_producer(SmemV11& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
-                                             const CUtensorMap* tmv, const UnitV1& u, int bh) {
-  int item = 1;                                            // item 0 (K0) and the Q tiles: k2_first_loads
+                                             const CUtensorMap* tmv, const UnitV1& u, int bh, V11Carry& c,
+                                             bool first_loads_done) {
   auto load_kv = [&](const CUtensorMap* tm, int j) {
     int row0, valid; key_tile(u.ks, u.n0, u.j_begin + j, row0, valid);
-    const int slot = item % kV11Stages;
-    mbar_wait(&sm.kv_empty[slot], ((item / kV11Stages) & 1) ^ 1);
+    const int slot = c.item % kV11Stages;
+    mbar_wait(&sm.kv_empty[slot], ((c.item / kV11Stages) & 1) ^ 1);
     k2_load_tile<SmemV11, kV11Stages>(sm.kv[slot], tm, &sm.kv_full[slot], row0, bh);
-    ++item;
+    ++c.item;
   };
   const int n = u.n_local;
+  if (first_loads_done) {
+    ++c.item;                                              // item 0 (K0) and the Q tiles: k2_first_loads
+  } else {
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      if (t < u.n_q) {
+        // the last QK of the unit before on this tile has read the old Q (persistent form)
+        if (c.units[t] > 0) mbar_wait(&sm.q_empty[t], (c.units[t] - 1) & 1);
+        k2_load_tile<SmemV11, kV11Stages>(sm.q[t], tmq, &sm.q_full[t], u.q_row0[t], bh);
+      }
+    }
+    load_kv(tmk, 0);
+  }
+  for (int t = 0; t < u.n_q; ++t) ++c.units[t];
   for (int j = 0; j < n; ++j) {
     if (j + 1 < n) load_kv(tmk, j + 1);
     load_kv(tmv, j);
   }
 }
 
-__device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1& u) {
+__device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1& u, V11Carry& c) {
   constexpr uint32_t idesc_qk = make_idesc_bf16(kBM, kBN, false, false);
   constexpr uint32_t idesc_pv = make_idesc_bf16(kBM, kD, false, true);
   const uint64_t dq = make_smem_desc(smem_u32(sm.q[0]), 16, 1024);
@@ -365,16 +390,15 @@ __device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1
   const uint64_t dv = make_smem_desc(smem_u32(sm.kv[0]), kHalfBytes, 1024);     // V tile: MN-major
   const bool two = u.n_q == 2;
   const int n = u.n_local;
-  int item = 0, n_qk = 0;
   auto kv_wait = [&]() {
-    const int slot = item % kV11Stages;
-    mbar_wait(&sm.kv_full[slot], (item / kV11Stages) & 1);
-    ++item;
+    const int slot = c.item % kV11Stages;
+    mbar_wait(&sm.kv_full[slot], (c.item / kV11Stages) & 1);
+    ++c.item;
     return slot;
   };
   auto qk = [&](int t, int kslot, int jj) {               // S = Q_t K(jj)^T
-    if (jj == 0) mbar_wait(&sm.q_full[t], 0);
-    if (n_qk > 0) mbar_wait(&sm.s_free, (n_qk - 1) & 1);  // the score tile before this one is in registers
+    if (jj == 0) mbar_wait(&sm.q_full[t], c.units[t] & 1);
+    if (c.n_qk > 0) mbar_wait(&sm.s_free, (c.n_qk - 1) & 1);   // the score tile before this one is in registers
     tc_fence_after();
     const uint64_t qa = dq + (uint64_t)(t * (kTileBytes >> 4)), ka = dk + (uint64_t)(kslot * (kTileBytes >> 4));
 #pragma unroll
@@ -383,13 +407,15 @@ __device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1
       mma_ss(tmem, qa + off, ka + off, idesc_qk, kk > 0);
     }
     mma_commit(&sm.s_full[t]);
-    ++n_qk;
+    ++c.n_qk;
+    if (jj == n - 1) mma_commit(&sm.q_empty[t]);           // Q_t may be replaced (persistent form)
   };
   auto pv = [&](int t, int vslot, int j) {               // O_t (+)= P_t V in two key halves (P in TMEM)
     const uint64_t va = dv + (uint64_t)(vslot * (kTileBytes >> 4));
+    const uint32_t par = (uint32_t)(c.steps[t] + j) & 1u;
 #pragma unroll
     for (int hf = 0; hf < 2; ++hf) {
-      mbar_wait(&sm.p_full[t][hf], j & 1);
+      mbar_wait(&sm.p_full[t][hf], par);
       tc_fence_after();
 #pragma unroll
       for (int kk = 4 * hf; kk < 4 * hf + 4; ++kk)
@@ -417,11 +443,14 @@ __device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1
     mma_commit(&sm.kv_empty[vs]);
   }
   mma_commit(&sm.o_done);
+  for (int t = 0; t < u.n_q; ++t) { c.steps[t] += n; ++c.units[t]; }
+  ++c.n_units;
 }
 
 template <int kPolyEvery>
 __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const UnitV1& u,
-                                            const AttnParams& p, int t, int b, int h) {
+                                            const AttnParams& p, int t, int b, int h, int step0 = 0,
+                                            int unit0 = 0) {
   const int warp_q = (threadIdx.x >> 5) & 3, lane = threadIdx.x & 31;
   const int row = warp_q * 32 + lane;
   const uint32_t lane_off = (uint32_t)(warp_q * 32) << 16;
@@ -439,7 +468,7 @@ __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const Un
 #pragma unroll 1
   for (int j = 0; j < n_local; ++j) {
     const int valid = j == jr0 ? vr0 : (j == jr1 && n1 > 0) ? vr1 : kBN;
-    mbar_wait(&sm.s_full[t], j & 1);
+    mbar_wait(&sm.s_full[t], (step0 + j) & 1);
     tc_fence_after();
     uint32_t s[kBN];
     tmem_ld32(t_s, s);
@@ -469,9 +498,9 @@ __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const Un
     const float mx = fmaxf(fmaxf(mc[0], mc[1]), fmaxf(mc[2], mc[3]));
     const bool grow = (mx - m_used) * scale > kRescaleThreshold;
     const float m_new = grow ? mx : m_used;
-    bool pv_waited = j == 0;
+    bool pv_waited = step0 + j == 0;
     if (j > 0 && __any_sync(0xffffffffu, grow)) {
-      mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+      mbar_wait(&sm.pv_done[t], (step0 + j - 1) & 1);
       tc_fence_after();
       pv_waited = true;
       const float alpha = grow ? ex2((m_used - m_new) * scale) : 1.f;
@@ -510,7 +539,7 @@ __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const Un
         pk[i] = pack2(e0, e1);
       }
       if (!pv_waited) {                                     // PV_t(j-1) has finished reading P_t
-        mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+        mbar_wait(&sm.pv_done[t], (step0 + j - 1) & 1);
         tc_fence_after();
         pv_waited = true;
       }
@@ -527,7 +556,7 @@ __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const Un
     }
   }
 
-  mbar_wait(&sm.o_done, 0);
+  mbar_wait(&sm.o_done, unit0 & 1);
   tc_fence_after();
   const float inv_l = 1.f / l_sum;
 #pragma unroll
@@ -565,6 +594,7 @@ attn_v11_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__
     }
     mbar_init(&sm.s_free, 4);
     mbar_init(&sm.o_done, 1);
+    mbar_init(&sm.q_empty[0], 1); mbar_init(&sm.q_empty[1], 1);
     fence_barrier_init();
     k2_first_loads<SmemV11, kV11Stages>(sm, &tmq, &tmk, u, bh);
   }
@@ -577,14 +607,96 @@ attn_v11_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__
   if (warp < 4) {
     setmaxnreg_dec<88>();
     if (warp == 0) {
-      if (elect_one()) v11_producer(sm, &tmq, &tmk, &tmv, u, bh);
+      if (elect_one()) { V11Carry c; v11_producer(sm, &tmq, &tmk, &tmv, u, bh, c, true); }
     } else if (warp == 1) {
-      if (elect_one()) v11_mma(sm, tmem, u);
+      if (elect_one()) { V11Carry c; v11_mma(sm, tmem, u, c); }
     }
   } else {
     setmaxnreg_inc<208>();
     const int t = (warp >> 2) - 1;
     if (t < u.n_q) v11_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+// =============================================================================
+// v11 persistent (CA_K2_V11P): one CTA per SM walks the flat unit list with a static stride and
+// calls the SAME role functions as v11 once per unit; only the mbarrier phase counters (V11Carry)
+// run on.  No extra synchronisation between units: every role simply runs ahead as far as its
+// barriers allow — the producer fetches the next unit's Q tiles (after q_empty: the last QK of the
+// unit before has read the old ones) and K/V while the last key steps are still in flight, the MMA
+// thread issues the next unit's first QK while the softmax warps drain O, and the next unit's first
+// PV cannot touch an unread accumulator because it waits for a p_full that the softmax warps arrive
+// on only after their epilogue (program order).  TMEM allocation, barrier init, tensor-map
+// prefetch and the CTA launch itself are paid once per SM instead of once per unit.
+// =============================================================================
+template <int kPolyEvery>
+__global__ void __launch_bounds__(384, 1)
+attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
+                 const __grid_constant__ CUtensorMap tmv, const AttnParams p, int total) {
+  extern __shared__ uint8_t smem_raw[];
+  SmemV11& sm = *reinterpret_cast<SmemV11*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int first = (int)blockIdx.x, stride = (int)gridDim.x;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
+    for (int i = 0; i < kV11Stages; ++i) { mbar_init(&sm.kv_full[i], 1); mbar_init(&sm.kv_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm.q_full[i], 1); mbar_init(&sm.q_empty[i], 1);
+      mbar_init(&sm.s_full[i], 1); mbar_init(&sm.pv_done[i], 1);
+      mbar_init(&sm.p_full[i][0], 4); mbar_init(&sm.p_full[i][1], 4);
+    }
+    mbar_init(&sm.s_free, 4);
+    mbar_init(&sm.o_done, 1);
+    fence_barrier_init();
+    const UnitV1 u0 = decode_unit(p, first);
+    if (u0.n_local > 0) k2_first_loads<SmemV11, kV11Stages>(sm, &tmq, &tmk, u0, u0.bh);
+  }
+  if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp < 4) {
+    setmaxnreg_dec<88>();
+    if (warp == 0) {
+      if (elect_one()) {
+        V11Carry c;
+#pragma unroll 1
+        for (int cta = first; cta < total; cta += stride) {
+          const UnitV1 u = decode_unit(p, cta);
+          if (u.n_local > 0) v11_producer(sm, &tmq, &tmk, &tmv, u, u.bh, c, cta == first);
+        }
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        V11Carry c;
+#pragma unroll 1
+        for (int cta = first; cta < total; cta += stride) {
+          const UnitV1 u = decode_unit(p, cta);
+          if (u.n_local > 0) v11_mma(sm, tmem, u, c);
+        }
+      }
+    }
+  } else {
+    setmaxnreg_inc<208>();
+    const int t = (warp >> 2) - 1;
+    int step0 = 0, unit0 = 0;
+#pragma unroll 1
+    for (int cta = first; cta < total; cta += stride) {
+      const UnitV1 u = decode_unit(p, cta);
+      if (u.n_local == 0) continue;
+      if (t < u.n_q) {
+        const int b = u.bh / p.H, h = u.bh - b * p.H;
+        v11_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h, step0, unit0);
+        step0 += u.n_local;
+      }
+      ++unit0;
+    }
   }
   tc_fence_before();
   __syncthreads();

@@ -139,10 +139,12 @@ ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v,
  *                        tile; the only one with the stream-K tail (uses `workspace`)
  *            CA_K2_V7    P through shared memory, a tile's score buffer is free once loaded
  *            CA_K2_V11   one score buffer shared by the two tiles, P in TMEM, five K/V stages
+ *            CA_K2_V11P  the same kernel persistent: one CTA per SM walks the unit list, the mbarrier
+ *                        phases run on from unit to unit (no TMEM / barrier set-up or CTA launch per unit)
  *   plan_sms 0 = plan the stream-K tail for the real SM count with the measured thresholds,
  *            < 0 = never split, n > 0 = plan for n SMs (parity tests of the tail on any GPU)
  * All kernels compute the same function to bf16 round-off; CA_ERR_INVALID_ARG for an unknown impl. */
-enum { CA_K2_AUTO = 0, CA_K2_V3 = 1, CA_K2_V7 = 2, CA_K2_V11 = 3 };
+enum { CA_K2_AUTO = 0, CA_K2_V3 = 1, CA_K2_V7 = 2, CA_K2_V11 = 3, CA_K2_V11P = 4 };
 size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,
                                              int impl, int plan_sms);
 ca_status ca_joint_attention_ex(const void* q, const void* k, const void* v,
