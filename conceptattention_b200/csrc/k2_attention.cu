@@ -696,11 +696,15 @@ extern "C" int ca_debug_streamk_piece(int n_steps, int sk_units, int sk_sms, int
   return ok ? 1 : 0;
 }
 
-// Which kernel a launch uses (include/conceptattention_b200.h): CA_K2_AUTO picks by key steps —
-// v11 up to 64 steps per unit, v7 beyond (measured, profiles/r02_k2_variants.md).
-static int resolve_impl(int impl, int n_steps) {
-  if (impl == CA_K2_AUTO) return n_steps <= 64 ? CA_K2_V11 : CA_K2_V7;
-  return impl;
+// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO, measured
+// (profiles/r02_k2_variants.md): v11 up to 64 key steps per query-tile unit, v7 beyond; the
+// persistent form of v11 when the units are short AND many (<= 16 key steps, >= 4 per SM: config 3,
+// +5 %) — with few or long units its static stride only adds imbalance (config 4: -4 %).
+static int resolve_impl(int impl, int n_steps, int64_t units = 0) {
+  if (impl != CA_K2_AUTO) return impl;
+  if (n_steps > 64) return CA_K2_V7;
+  if (n_steps <= 16 && units >= 4 * 148) return CA_K2_V11P;
+  return CA_K2_V11;
 }
 
 extern "C" size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,
@@ -769,7 +773,7 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   if ((s = make_qkv_tmap(&tmv, v, B * H, Ntot, kBN)) != CA_OK) return s;
 
   const bool concept_attn = C > 0 && mode != CA_ATTN_NEITHER;
-  const int kernel = resolve_impl(impl, p.n_main_tiles);
+  const int kernel = resolve_impl(impl, p.n_main_tiles, (int64_t)p.n_pairs * B * H);
   const int W = p.n_pairs * B * H;
   p.n_concept = concept_attn ? B * H : 0;
   const size_t need = ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, impl, plan_sms);

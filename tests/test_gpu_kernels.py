@@ -205,12 +205,12 @@ def test_joint_attention_stream_k_tail(ops, B, H, P, T, C, sms):
         assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1])
 
 
-@pytest.mark.parametrize("impl", ["V3", "V7", "V11"])
+@pytest.mark.parametrize("impl", ["V3", "V7", "V11", "V11P"])
 @pytest.mark.parametrize("B,H,P,T,C,mode", [(1, 2, 1024, 256, 32, 0), (2, 3, 256, 256, 4, 0), (1, 2, 2200, 200, 5, 0),
                                             (1, 1, 200, 100, 1, 0), (1, 2, 144, 72, 3, 1), (1, 2, 100, 20, 3, 2),
                                             (2, 2, 0, 130, 0, 0), (8, 24, 256, 128, 2, 0)])
 def test_joint_attention_every_kernel_matches_oracle(ops, impl, B, H, P, T, C, mode):
-    """ca_joint_attention_ex with each kernel named per call (CA_K2_V3 / V7 / V11): same function to
+    """ca_joint_attention_ex with each kernel named per call (CA_K2_V3 / V7 / V11 / V11P): same function to
     bf16 round-off — also with scores that keep growing along the keys (forces the lazy O rescale
     on many tiles), one-tile units, ragged key tiles in both key segments, and more concept
     units than SMs (8 x 24 of them: CTAs that follow a one-tile CTA on the same SM)."""
