@@ -37,6 +37,7 @@ SIGNATURES = {
     "ca_heatmap_accumulate": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p],
     "ca_heatmap_accumulate_pair": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p,
                                    _i64, _p, _i, _p],
+    "ca_heatmap_accumulate_both": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _p, _i, _p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _p, _i, _i, _i, _i, _i, _i, _p, _i64, _p, _p],
     "ca_norm_accumulate_pair": [_p, _i, _i, _i, _i, _i, _p, _p, _p],
     "ca_heatmap_logits": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _p, _p],
     "ca_norm_accumulate": [_p, _i, _i, _i, _i, _i, _p, _p],

@@ -87,5 +87,6 @@ __device__ __forceinline__ float* pair_base(const HmArgs& a) {
 // tcgen05/TMA variant (k3_heatmap_tc.cu).  Returns CA_ERR_UNSUPPORTED when the shape does not
 // fit it (seg_len % 64 != 0, ...): the caller then uses the SIMT kernel.
 ca_status launch_heatmap_tc(const HmArgs& a, bool logits_only, cudaStream_t st);
+ca_status launch_heatmap_tc_dual(const HmArgs& a, const HmArgs& b, cudaStream_t st);
 
 }  // namespace ca

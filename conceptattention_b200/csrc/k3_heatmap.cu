@@ -194,6 +194,43 @@ extern "C" ca_status ca_heatmap_accumulate_pair(const void* img, int64_t isb, in
   return ca::launch_heatmap<false>(a, (cudaStream_t)stream);
 }
 
+// Output-space and cross-attention-space maps of one layer in ONE launch (gridDim.z = 2 of the
+// TMA/tcgen05 kernel) when both fit it; otherwise the two launches of ca_heatmap_accumulate_pair.
+extern "C" ca_status ca_heatmap_accumulate_both(
+    const void* img0, int64_t isb0, int64_t iss0, int64_t isp0, const void* con0, int64_t csb0, int64_t css0,
+    int64_t csc0, int nseg0, int seg_len0, float* acc0, int pair_slot_off0,
+    const void* img1, int64_t isb1, int64_t iss1, int64_t isp1, const void* con1, int64_t csb1, int64_t css1,
+    int64_t csc1, int nseg1, int seg_len1, float* acc1, int pair_slot_off1,
+    int B, int P, int C, int norm, int round_bf16, float* pair, int64_t pair_stride, const int* pair_slot,
+    void* stream) {
+  ca::HmArgs a{(const __nv_bfloat16*)img0, isb0, iss0, isp0, (const __nv_bfloat16*)con0, csb0, css0, csc0,
+               nseg0, seg_len0, B, P, C, norm, round_bf16, acc0};
+  ca::HmArgs b{(const __nv_bfloat16*)img1, isb1, iss1, isp1, (const __nv_bfloat16*)con1, csb1, css1, csc1,
+               nseg1, seg_len1, B, P, C, norm, round_bf16, acc1};
+  a.pair = b.pair = pair; a.pair_stride = b.pair_stride = pair_stride; a.pair_slot = b.pair_slot = pair_slot;
+  a.pair_slot_off = pair_slot_off0; b.pair_slot_off = pair_slot_off1;
+  if (pair && pair_stride < (int64_t)B * C * P) return CA_ERR_INVALID_ARG;
+  const ca::HmArgs* both[2] = {&a, &b};
+  bool fits = true;
+  for (const ca::HmArgs* x : both) {
+    if (!x->img || !x->con || !x->acc || B < 0 || P < 0 || C <= 0 || x->nseg <= 0 || x->seg_len <= 0)
+      return CA_ERR_INVALID_ARG;
+    if (C > CA_MAX_CONCEPTS || x->seg_len % 8) return CA_ERR_UNSUPPORTED;
+    if (!ca::aligned16(x->img) || !ca::aligned16(x->con) ||
+        (x->isb | x->iss | x->isp | x->csb | x->css | x->csc) % 8)
+      return CA_ERR_ALIGNMENT;
+  }
+  if (norm < CA_NORM_SOFTMAX || norm > CA_NORM_NONE) return CA_ERR_INVALID_ARG;
+  if (B == 0 || P == 0) return CA_OK;
+  if (fits) {
+    const ca_status s = ca::launch_heatmap_tc_dual(a, b, (cudaStream_t)stream);
+    if (s != CA_ERR_UNSUPPORTED) return s;
+  }
+  ca_status s = ca::launch_heatmap<false>(a, (cudaStream_t)stream);
+  if (s != CA_OK) return s;
+  return ca::launch_heatmap<false>(b, (cudaStream_t)stream);
+}
+
 extern "C" ca_status ca_heatmap_logits(const void* img, int64_t isb, int64_t iss, int64_t isp,
                                        const void* con, int64_t csb, int64_t css, int64_t csc,
                                        int nseg, int seg_len, int B, int P, int C, float* logits,

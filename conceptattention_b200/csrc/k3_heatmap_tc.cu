@@ -46,8 +46,15 @@ struct HmTcParams {
 
 template <int NPAD, int CT, bool kLogitsOnly>
 __global__ void __launch_bounds__(192)
-heatmap_tc_kernel(const __grid_constant__ CUtensorMap tma, const __grid_constant__ CUtensorMap tmb,
-                  const HmTcParams p) {
+heatmap_tc_kernel(const __grid_constant__ CUtensorMap tma0, const __grid_constant__ CUtensorMap tmb0,
+                  const __grid_constant__ CUtensorMap tma1, const __grid_constant__ CUtensorMap tmb1,
+                  const HmTcParams p0, const HmTcParams p1) {
+  // blockIdx.z selects one of two independent problems of the same (B, P, C, K): the output-space
+  // and the cross-attention-space maps of one layer go out in ONE launch (gridDim.z = 2)
+  const bool second = blockIdx.z != 0;
+  const CUtensorMap* tma = second ? &tma1 : &tma0;
+  const CUtensorMap* tmb = second ? &tmb1 : &tmb0;
+  const HmTcParams& p = second ? p1 : p0;
   extern __shared__ uint8_t smem_raw[];
   SmemTc<NPAD>& sm = *reinterpret_cast<SmemTc<NPAD>*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -62,7 +69,7 @@ heatmap_tc_kernel(const __grid_constant__ CUtensorMap tma, const __grid_constant
   constexpr uint32_t kTmemCols = NPAD < 32 ? 32 : NPAD;
 
   if (threadIdx.x == 0) {
-    prefetch_tmap(&tma); prefetch_tmap(&tmb);
+    prefetch_tmap(tma); prefetch_tmap(tmb);
     for (int i = 0; i < kTcStages; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
     mbar_init(&sm.acc_done, 1);
     fence_barrier_init();
@@ -84,8 +91,8 @@ heatmap_tc_kernel(const __grid_constant__ CUtensorMap tma, const __grid_constant
         int ci = i + kshift; ci = ci >= n ? ci - n : ci;
         const int e = (chunk0 + ci) * 64, seg = e / p.seg_len, off = e - seg * p.seg_len;
         mbar_expect_tx(&sm.full[st], kTcABytes + NPAD * 128);
-        tma_load_4d(sm.pipe.a[st], &tma, &sm.full[st], off, row0, seg, b);
-        tma_load_4d(sm.pipe.b[st], &tmb, &sm.full[st], off, 0, seg, b);
+        tma_load_4d(sm.pipe.a[st], tma, &sm.full[st], off, row0, seg, b);
+        tma_load_4d(sm.pipe.b[st], tmb, &sm.full[st], off, 0, seg, b);
       }
     }
   } else if (warp == 1) {
@@ -182,12 +189,13 @@ static bool make_tmap4(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d
 
 template <int NPAD, int CT, bool kLogitsOnly>
 static ca_status launch_tc(const CUtensorMap& tma, const CUtensorMap& tmb, const HmTcParams& p,
-                           int tiles, int S, cudaStream_t st) {
+                           int tiles, int S, cudaStream_t st, const CUtensorMap* tma1 = nullptr,
+                           const CUtensorMap* tmb1 = nullptr, const HmTcParams* p1 = nullptr) {
   auto kern = heatmap_tc_kernel<NPAD, CT, kLogitsOnly>;
   const int smem = (int)sizeof(SmemTc<NPAD>) + 1024;
   CA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(tiles * S, p.B);
+  cfg.gridDim = dim3(tiles * S, p.B, p1 ? 2 : 1);
   cfg.blockDim = dim3(192);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
@@ -195,7 +203,7 @@ static ca_status launch_tc(const CUtensorMap& tma, const CUtensorMap& tmb, const
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  CA_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tma, tmb, p));
+  CA_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tma, tmb, tma1 ? *tma1 : tma, tmb1 ? *tmb1 : tmb, p, p1 ? *p1 : p));
   return CA_OK;
 }
 
@@ -225,6 +233,38 @@ ca_status launch_heatmap_tc(const HmArgs& a, bool logits_only, cudaStream_t st) 
   if (a.C <= 16) return CA_TC(16, 16);
   return CA_TC(32, 32);
 #undef CA_TC
+}
+
+// Two problems of the same (B, P, C, total K, norm) in one launch; CA_ERR_UNSUPPORTED when either
+// does not fit the TMA/tcgen05 kernel (the caller then launches them one by one).
+ca_status launch_heatmap_tc_dual(const HmArgs& a, const HmArgs& b, cudaStream_t st) {
+  if (a.B != b.B || a.P != b.P || a.C != b.C || a.norm != b.norm || a.round_bf16 != b.round_bf16 ||
+      a.nseg * a.seg_len != b.nseg * b.seg_len)
+    return CA_ERR_UNSUPPORTED;
+  if (a.seg_len % 64 || b.seg_len % 64 || a.C > 32 || a.P < 1 || a.B > 65535) return CA_ERR_UNSUPPORTED;
+  const int chunks = a.nseg * (a.seg_len / 64);
+  const int tiles = (a.P + kTcRows - 1) / kTcRows;
+  const int npad = a.C <= 16 ? 16 : 32;
+  CUtensorMap ta, tb, ua, ub;
+  if (!make_tmap4(&ta, a.img, a.seg_len, a.P, a.nseg, a.B, a.isp, a.iss, a.isb, kTcRows) ||
+      !make_tmap4(&tb, a.con, a.seg_len, a.C, a.nseg, a.B, a.csc, a.css, a.csb, npad) ||
+      !make_tmap4(&ua, b.img, b.seg_len, b.P, b.nseg, b.B, b.isp, b.iss, b.isb, kTcRows) ||
+      !make_tmap4(&ub, b.con, b.seg_len, b.C, b.nseg, b.B, b.csc, b.css, b.csb, npad))
+    return CA_ERR_UNSUPPORTED;
+  int S = 1;                                           // twice the CTAs of a single launch: split K less
+  const int smax = npad == 32 ? 4 : 8;
+  while (S < smax && (int64_t)tiles * a.B * S * 2 < 128 && chunks % (2 * S) == 0 && chunks / (2 * S) >= 2)
+    S *= 2;
+  HmTcParams pa{a.B, a.P, a.C, a.seg_len, chunks / S, a.norm, a.round_bf16, a.acc,
+                a.pair, a.pair_stride, a.pair_slot, a.pair_slot_off};
+  HmTcParams pb{b.B, b.P, b.C, b.seg_len, chunks / S, b.norm, b.round_bf16, b.acc,
+                b.pair, b.pair_stride, b.pair_slot, b.pair_slot_off};
+#define CA_TC2(NP, CT) launch_tc<NP, CT, false>(ta, tb, pa, tiles, S, st, &ua, &ub, &pb)
+  if (a.C <= 4) return CA_TC2(16, 4);
+  if (a.C <= 8) return CA_TC2(16, 8);
+  if (a.C <= 16) return CA_TC2(16, 16);
+  return CA_TC2(32, 32);
+#undef CA_TC2
 }
 
 }  // namespace ca

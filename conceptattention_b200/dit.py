@@ -118,10 +118,14 @@ class HeatmapAccumulator:
         """attn_img [B,P,D]; attn_con [B,C,D] view; q_pre [B,H,P+T+C,128]."""
         m = self.multiplicity(layer)
         for rep in range(m):
-            kw = (lambda s: self._pair_args(layer, s)) if rep == 0 else (lambda s: {})
-            ops.heatmap_accumulate(attn_img, attn_con, self.acc[0], self.norm, self.round_bf16, **kw(0))
-            ops.heatmap_accumulate(q_pre[:, :, :P], q_pre[:, :, P + T:], self.acc[1], self.norm,
-                                   self.round_bf16, per_head=True, **kw(1))
+            # output space and cross-attention space of this layer in ONE launch
+            kw = {}
+            if rep == 0 and self.pairs is not None:
+                a0, a1 = self._pair_args(layer, 0), self._pair_args(layer, 1)
+                kw = dict(pair=a0["pair"], pair_slot=a0["pair_slot"],
+                          pair_slot_off=(a0["pair_slot_off"], a1["pair_slot_off"]))
+            ops.heatmap_accumulate_both(attn_img, attn_con, self.acc[0], q_pre[:, :, :P], q_pre[:, :, P + T:],
+                                        self.acc[1], self.norm, self.round_bf16, **kw)
         self.count += m
 
     def signature(self, depth):

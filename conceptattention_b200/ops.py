@@ -335,6 +335,32 @@ def heatmap_logits(img, con, per_head=False, out=None):
     return out
 
 
+def heatmap_accumulate_both(img0, con0, acc0, img1, con1, acc1, norm="softmax", round_bf16=False,
+                            pair=None, pair_slot=None, pair_slot_off=(0, 1)):
+    """Both spaces of one layer in one launch: (img0 [B,P,K], con0 [B,C,K]) -> acc0 and the per-head
+    views (img1 [B,H,P,d], con1 [B,H,C,d]) -> acc1; same maths as two `heatmap_accumulate` calls."""
+    B, P, C, n0, l0, si0, sc0 = _hm_strides(img0, con0, False)
+    B1, P1, C1, n1, l1, si1, sc1 = _hm_strides(img1, con1, True)
+    assert (B, P, C) == (B1, P1, C1) and n0 * l0 == n1 * l1
+    for a in (acc0, acc1):
+        _req(a, torch.float32, "acc")
+        assert a.shape == (B, C, P)
+    pstride = 0
+    if pair is not None:
+        _req(pair, torch.float32, "pair")
+        assert pair.dim() == 4 and pair.shape[1:] == (B, C, P)
+        pstride = pair.stride(0)
+    K = n0 * l0
+    with _timed(f"K3+K4 heatmap_accumulate both spaces rows={B * P}",
+                2 * B * (2 * P * K + 2 * C * K + (8 if pair is None else 12) * C * P)):
+        check(_cabi.load().ca_heatmap_accumulate_both(
+            img0.data_ptr(), *si0, con0.data_ptr(), *sc0, n0, l0, acc0.data_ptr(), pair_slot_off[0],
+            img1.data_ptr(), *si1, con1.data_ptr(), *sc1, n1, l1, acc1.data_ptr(), pair_slot_off[1],
+            B, P, C, NORM[norm], int(round_bf16), pair.data_ptr() if pair is not None else None, pstride,
+            pair_slot.data_ptr() if pair_slot is not None else None, _stream(img0)),
+            "ca_heatmap_accumulate_both")
+
+
 def norm_accumulate(logits, acc, norm="softmax", round_bf16=False, pair=None):
     """acc += norm_c(logits); `pair` (fp32 [B,C,P], optional) also receives norm_c(logits)."""
     _req(logits, torch.float32, "logits"); _req(acc, torch.float32, "acc")

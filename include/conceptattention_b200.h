@@ -186,6 +186,21 @@ ca_status ca_heatmap_accumulate_pair(const void* img, int64_t img_stride_b, int6
                                      int64_t pair_stride, const int* pair_slot_dev,
                                      int pair_slot_off, void* stream);
 
+/* Both spaces of one layer in ONE launch: problem 0 (output space: img0 / con0, nseg0 = 1) and
+ * problem 1 (cross-attention space: the pre-RoPE queries, nseg1 = H) share B, P, C, the total vector
+ * length nseg * seg_len, the normaliser and the per-pair buffer; each has its own accumulator and
+ * its own slot offset.  Same results as two ca_heatmap_accumulate_pair calls (which is what this
+ * entry does when a problem does not fit the TMA/tcgen05 kernel). */
+ca_status ca_heatmap_accumulate_both(
+    const void* img0, int64_t img0_stride_b, int64_t img0_stride_s, int64_t img0_stride_p,
+    const void* con0, int64_t con0_stride_b, int64_t con0_stride_s, int64_t con0_stride_c,
+    int nseg0, int seg_len0, float* acc0, int pair_slot_off0,
+    const void* img1, int64_t img1_stride_b, int64_t img1_stride_s, int64_t img1_stride_p,
+    const void* con1, int64_t con1_stride_b, int64_t con1_stride_s, int64_t con1_stride_c,
+    int nseg1, int seg_len1, float* acc1, int pair_slot_off1,
+    int B, int P, int C, int norm, int round_bf16, float* pair, int64_t pair_stride,
+    const int* pair_slot_dev, void* stream);
+
 /* K3 only: partial logits of a head/feature slice, written (not accumulated) as
  * fp32 [B,C,P] — the buffer a head-sharded run all-reduces before K4. */
 ca_status ca_heatmap_logits(const void* img, int64_t img_stride_b, int64_t img_stride_s,

@@ -165,3 +165,29 @@ def test_heatmaps_from_vectors_host_matches_reference(golden_dir):
         torch.testing.assert_close(heat, ref_bf16_inputs, rtol=1e-4, atol=1e-5)
         golden = torch.from_numpy(g[tag + "_softmax"]).reshape(B, C, P)   # reference, fp32 inputs
         assert ((heat - golden).abs() / golden.clamp_min(1e-3)).max() < 5e-2
+
+
+@pytest.mark.parametrize("B,P,C,H,T,pairs", [(1, 4096, 4, 24, 256, False), (2, 1000, 20, 24, 8, True),
+                                             (1, 300, 32, 8, 4, False), (1, 200, 3, 2, 0, True)])
+def test_both_spaces_in_one_launch_equal_two_launches(ops, B, P, C, H, T, pairs):
+    """ca_heatmap_accumulate_both (output space + cross-attention space of one layer, gridDim.z = 2)
+    against the two single-space launches it replaces: accumulators and per-pair slots, the
+    per-head view of the packed q_pre, a vector length the TMA kernel does not take (H = 2 -> SIMT)."""
+    D = H * 128
+    img, con = rnd(B, P, D, seed=21).cuda(), rnd(B, C, D, seed=22, scale=3.0 / math.sqrt(D)).cuda()
+    q_pre = rnd(B, H, P + T + C, 128, seed=23, scale=0.3).cuda()
+    qi, qc = q_pre[:, :, :P], q_pre[:, :, P + T:]
+    acc_a = torch.full((2, B, C, P), 0.25, device="cuda")
+    acc_b = acc_a.clone()
+    slots = torch.zeros(6, B, C, P, device="cuda") if pairs else None
+    slots_b = None if slots is None else slots.clone()
+    slot = torch.full((1,), 2, device="cuda", dtype=torch.int32) if pairs else None
+    for norm in ("softmax", "sparsemax"):
+        ops.heatmap_accumulate(img, con, acc_a[0], norm, pair=slots, pair_slot=slot, pair_slot_off=0)
+        ops.heatmap_accumulate(qi, qc, acc_a[1], norm, per_head=True, pair=slots, pair_slot=slot, pair_slot_off=1)
+        ops.heatmap_accumulate_both(img, con, acc_b[0], qi, qc, acc_b[1], norm, pair=slots_b, pair_slot=slot,
+                                    pair_slot_off=(0, 1))
+    torch.testing.assert_close(acc_b, acc_a, rtol=1e-5, atol=1e-6)
+    if pairs:
+        torch.testing.assert_close(slots_b, slots, rtol=1e-5, atol=1e-6)
+        assert slots_b[2].abs().sum() > 0 and slots_b[3].abs().sum() > 0 and slots_b[0].abs().sum() == 0
