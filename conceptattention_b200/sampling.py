@@ -159,7 +159,7 @@ def apply_colormap(x01, cmap="plasma"):
     try:
         import matplotlib.pyplot as plt
         return (plt.get_cmap(cmap)(x01)[:, :, :3] * 255).astype(np.uint8)
-    except ImportError:
+    except (ImportError, AttributeError):       # absent, or a stub module someone put in sys.modules
         if cmap != "plasma":
             raise ValueError(f"cmap={cmap!r} needs matplotlib; only 'plasma' is built in")
         x = np.asarray(x01, dtype=np.float64)

@@ -187,7 +187,8 @@ def test_both_spaces_in_one_launch_equal_two_launches(ops, B, P, C, H, T, pairs)
         ops.heatmap_accumulate(qi, qc, acc_a[1], norm, per_head=True, pair=slots, pair_slot=slot, pair_slot_off=1)
         ops.heatmap_accumulate_both(img, con, acc_b[0], qi, qc, acc_b[1], norm, pair=slots_b, pair_slot=slot,
                                     pair_slot_off=(0, 1))
-    torch.testing.assert_close(acc_b, acc_a, rtol=1e-5, atol=1e-6)
+    # same kernel, but twice the CTAs per launch -> a smaller split-K factor -> another fp32 summation order
+    torch.testing.assert_close(acc_b, acc_a, rtol=5e-5, atol=2e-5)
     if pairs:
-        torch.testing.assert_close(slots_b, slots, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(slots_b, slots, rtol=5e-5, atol=2e-5)
         assert slots_b[2].abs().sum() > 0 and slots_b[3].abs().sum() > 0 and slots_b[0].abs().sum() == 0
