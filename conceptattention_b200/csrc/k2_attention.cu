@@ -696,15 +696,16 @@ extern "C" int ca_debug_streamk_piece(int n_steps, int sk_units, int sk_sms, int
   return ok ? 1 : 0;
 }
 
-// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO, measured
-// (profiles/r02_k2_variants.md): v11 up to 64 key steps per query-tile unit, v7 beyond; the
-// persistent form of v11 when the units are short AND many (<= 16 key steps, >= 4 per SM: config 3,
-// +5 %) — with few or long units its static stride only adds imbalance (config 4: -4 %).
+// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO, measured on B200 (148 SMs;
+// three alternating runs of 60 launches each, profiles/r02_k2_variants.md): the persistent form of v11
+// up to 64 key steps per query-tile unit (config 2 +2 %, config 4 +6 %, config 3 +8 % over the
+// one-unit-per-CTA v11) and for longer units when there are fewer than two waves of them (3 heads x
+// 16.6K rows: 0.41-0.45 ms against 0.45-0.53 for v7); v7 for long units in many waves (config 5 on one
+// or two GPUs: 2-5 % ahead of v11p).
 static int resolve_impl(int impl, int n_steps, int64_t units = 0) {
   if (impl != CA_K2_AUTO) return impl;
-  if (n_steps > 64) return CA_K2_V7;
-  if (n_steps <= 16 && units >= 4 * 148) return CA_K2_V11P;
-  return CA_K2_V11;
+  if (n_steps <= 64) return CA_K2_V11P;
+  return units < 2 * 148 ? CA_K2_V11P : CA_K2_V7;
 }
 
 extern "C" size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,

@@ -272,7 +272,7 @@ __device__ __forceinline__ void v7_softmax(SmemV7& sm, uint32_t tmem, const Unit
   }
 }
 
-template <int kPolyEvery>
+template <int kPolyEvery, int kCtlRegs = 88, int kSmxRegs = 208>
 __global__ void __launch_bounds__(384, 1)
 attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
@@ -303,14 +303,14 @@ attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
 
   if (warp < 4) {
     // register pool of a 384-thread CTA: 384 x 168 = 64512 = 128 x 88 + 256 x 208
-    setmaxnreg_dec<88>();
+    setmaxnreg_dec<kCtlRegs>();
     if (warp == 0) {
       if (elect_one()) v7_producer(sm, &tmq, &tmk, &tmv, u, bh);
     } else if (warp == 1) {
       if (elect_one()) v7_mma(sm, tmem, u);
     }
   } else {
-    setmaxnreg_inc<208>();
+    setmaxnreg_inc<kSmxRegs>();
     const int t = (warp >> 2) - 1;
     if (t < u.n_q) v7_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
   }
@@ -573,7 +573,7 @@ __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const Un
   }
 }
 
-template <int kPolyEvery>
+template <int kPolyEvery, int kCtlRegs = 104, int kSmxRegs = 200>
 __global__ void __launch_bounds__(384, 1)
 attn_v11_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmk,
                 const __grid_constant__ CUtensorMap tmv, const AttnParams p) {
@@ -605,14 +605,14 @@ attn_v11_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__
   const uint32_t tmem = sm.tmem_base;
 
   if (warp < 4) {
-    setmaxnreg_dec<88>();
+    setmaxnreg_dec<kCtlRegs>();
     if (warp == 0) {
       if (elect_one()) { V11Carry c; v11_producer(sm, &tmq, &tmk, &tmv, u, bh, c, true); }
     } else if (warp == 1) {
       if (elect_one()) { V11Carry c; v11_mma(sm, tmem, u, c); }
     }
   } else {
-    setmaxnreg_inc<208>();
+    setmaxnreg_inc<kSmxRegs>();
     const int t = (warp >> 2) - 1;
     if (t < u.n_q) v11_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h);
   }
@@ -662,7 +662,7 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
   const uint32_t tmem = sm.tmem_base;
 
   if (warp < 4) {
-    setmaxnreg_dec<88>();
+    setmaxnreg_dec<104>();
     if (warp == 0) {
       if (elect_one()) {
         V11Carry c;
@@ -683,7 +683,7 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
       }
     }
   } else {
-    setmaxnreg_inc<208>();
+    setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
     int step0 = 0, unit0 = 0;
 #pragma unroll 1
