@@ -47,6 +47,9 @@ struct AttnParams {
   int n_concept;                       // concept units (one per (b,h)) or 0
   float* ws_part;                      // [2*sk_sms] partial slots (kPartFloats each)
   int* ws_count;                       // [sk_units] arrival counters (zeroed by the launcher)
+  // persistent v11 only: key-step ranges instead of whole units (k2_attention_v7.cuh, "v11p stream-K")
+  int skp_on;                          // 1: CTA c works on main key steps [B(c), B(c+1))
+  int skp_wc;                          // cost of one concept unit in main key steps (balancing weight)
 };
 
 // one partial slot: per query tile an unnormalised fp32 O (stored [col/4][row][4] so that the 32
@@ -708,12 +711,54 @@ static int resolve_impl(int impl, int n_steps, int64_t units = 0) {
   return units < 2 * 148 ? CA_K2_V11P : CA_K2_V7;
 }
 
+namespace ca {
+static int sm_count_cached() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      n = 0;
+  }
+  return n;
+}
+// Key-step ranges for the persistent v11 (see SkpIter): on when whole units would leave the last
+// wave at least 8 % longer than an even split of the work, and a CTA's share is at least 8 key steps.
+struct SkpPlan { bool on; int G, wc; int64_t W; };
+static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode) {
+  SkpPlan pl{false, 0, 0, 0};
+  const int sms = sm_count_cached();
+  if (sms <= 0 || B <= 0 || H <= 0 || P + T <= 0) return pl;
+  const int n = (P + T + kBM - 1) / kBM;
+  const int64_t W = (int64_t)((n + 1) / 2) * B * H;
+  const int64_t n_concept = (C > 0 && mode != CA_ATTN_NEITHER) ? (int64_t)B * H : 0;
+  int nc = 0;                                              // key tiles of a concept unit
+  if (n_concept) {
+    if (mode != CA_ATTN_SELF_ONLY) nc += (P + kBN - 1) / kBN;
+    if (mode != CA_ATTN_CROSS_ONLY) nc += (C + kBN - 1) / kBN;
+  }
+  pl.W = W; pl.G = sms; pl.wc = (2 * nc + 2) / 3;          // one tile per step instead of two: ~2/3 of the cost
+  const int64_t T_cost = W * n + n_concept * pl.wc;
+  const int64_t whole = ((W + n_concept + sms - 1) / sms) * n;
+  pl.on = W * n >= (int64_t)8 * sms && whole * sms * 100 >= T_cost * 108 && W * n < 0x7fffffffLL;
+  return pl;
+}
+static size_t skp_workspace_bytes(const SkpPlan& pl) {
+  return (size_t)2 * pl.G * kPartFloats * sizeof(float) + (size_t)2 * pl.W * sizeof(int) + 256;
+}
+}  // namespace ca
+
 extern "C" size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,
                                                         int impl, int plan_sms) {
   using namespace ca;
   if (B <= 0 || H <= 0 || P + T <= 0) return 0;
   const int n_main = (P + T + kBM - 1) / kBM;
-  if (resolve_impl(impl, n_main) != CA_K2_V3) return 0;     // only v3 has the stream-K tail
+  const int which = resolve_impl(impl, n_main, (int64_t)((n_main + 1) / 2) * B * H);
+  if (which == CA_K2_V11P && plan_sms >= 0) {                 // key-step ranges of the persistent kernel
+    const SkpPlan sp = plan_v11p(B, H, P, T, C, mode);
+    return sp.on ? skp_workspace_bytes(sp) : 0;
+  }
+  if (which != CA_K2_V3) return 0;
   const int n_concept = (C > 0 && mode != CA_ATTN_NEITHER) ? B * H : 0;
   const SkPlan pl = plan_streamk(((n_main + 1) / 2) * B * H, n_concept, n_main, true, plan_sms);
   if (pl.sk_sms == 0) return 0;
@@ -766,6 +811,7 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   p.scale_log2 = kLog2e / sqrtf((float)kD);
   p.n_pairs = (p.n_main_tiles + 1) / 2;
   p.ws_part = nullptr; p.ws_count = nullptr;
+  p.skp_on = 0; p.skp_wc = 0;
 
   CUtensorMap tmq, tmk, tmv;
   ca_status s;
@@ -792,6 +838,13 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   if (ctas > 0) {
     // every kernel: polynomial exp2 on every 4th element pair (the MUFU / FMA-pipe balance point)
     if (kernel == CA_K2_V11P) {
+      const SkpPlan sp = plan_v11p(B, H, P, T, C, mode);
+      if (sp.on && plan_sms >= 0 && workspace != nullptr && workspace_bytes >= skp_workspace_bytes(sp)) {
+        p.skp_on = 1; p.skp_wc = sp.wc;
+        p.ws_part = (float*)workspace;
+        p.ws_count = (int*)((char*)workspace + (size_t)2 * sp.G * kPartFloats * sizeof(float));
+        CA_CUDA_OK(cudaMemsetAsync(p.ws_count, 0, (size_t)2 * sp.W * sizeof(int), st));
+      }
       static bool configured = false;
       static int sms = 0;
       const int smem = (int)sizeof(SmemV11) + 1024;
@@ -802,7 +855,7 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
         CA_CUDA_OK(cudaFuncSetAttribute(attn_v11p_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
       }
-      attn_v11p_kernel<4><<<(unsigned)(ctas < sms ? ctas : sms), 384, smem, st>>>(tmq, tmk, tmv, p, (int)ctas);
+      attn_v11p_kernel<4><<<(unsigned)(p.skp_on || ctas >= sms ? sms : ctas), 384, smem, st>>>(tmq, tmk, tmv, p, (int)ctas);
       CA_LAUNCH_CHECK();
       s = CA_OK;
     } else if (kernel == CA_K2_V11) s = launch_k2<attn_v11_kernel<4>>((int)sizeof(SmemV11) + 1024, ctas, st, tmq, tmk, tmv, p);

@@ -339,6 +339,7 @@ struct SmemV11 {
   uint64_t s_full[2], s_free, p_full[2][2], pv_done[2], o_done;
   uint64_t q_empty[2];                                      // persistent form only
   uint32_t tmem_base;
+  int sk_flag[2];                                           // stream-K: "this piece merges" per tile
 };
 
 // Phase counters that run on from unit to unit in the persistent form (all zero for a
@@ -350,6 +351,82 @@ struct V11Carry {
   int units[2] = {0, 0};   // units so far that used tile t: q_full / q_empty phases
   int n_units = 0;     // units so far: o_done phases
 };
+
+// ---- v11p stream-K: key-step ranges ---------------------------------------------------------
+// With skp_on the G persistent CTAs do not take whole main units: the W * n key steps of the W
+// main units (n = key tiles per unit) are one stream and CTA c works on steps [B(c), B(c+1)) of it,
+// after its share of the (whole) concept units c, c + G, ...  B(c) = running max over i <= c of
+// floor(i * T / G) - C(i), with T = W * n + n_concept * wc the total cost and C(i) the concept cost
+// of CTAs 0..i-1, so a CTA that also runs a concept unit gets that many fewer main steps.  A unit
+// cut by a boundary is worked on by two (or more) CTAs: each piece leaves (O unnormalised, row max,
+// row sum) per tile in its CTA's slot and the piece that finishes last merges — v3's fix-up, with
+// the pieces of one range run back to back by ONE CTA.
+struct SkpIter {                                          // incremental B(i), i = 0, 1, 2, ...
+  int64_t T, Sm, conc, best;
+  int i, G, n_concept, wc;
+  __device__ __forceinline__ void init(const AttnParams& p, int G_) {
+    G = G_; n_concept = p.n_concept; wc = p.skp_wc;
+    Sm = (int64_t)p.n_dp * p.n_main_tiles;
+    T = Sm + (int64_t)n_concept * wc;
+    conc = 0; best = 0; i = 0;
+  }
+  __device__ __forceinline__ int64_t bound() const {       // B(i)
+    if (i >= G) return Sm;
+    const int64_t v = (int64_t)i * T / G - conc;
+    const int64_t b = v > best ? v : best;
+    return b < Sm ? b : Sm;
+  }
+  __device__ __forceinline__ void step() {                 // i -> i + 1
+    const int64_t v = (int64_t)i * T / G - conc;
+    if (v > best) best = v;
+    if (i < n_concept) conc += (int64_t)((n_concept - i + G - 1) / G) * wc;
+    ++i;
+  }
+};
+
+__device__ __forceinline__ void skp_range(const AttnParams& p, int G, int c, int64_t& lo, int64_t& hi) {
+  SkpIter it; it.init(p, G);
+  for (int k = 0; k < c; ++k) it.step();
+  lo = it.bound(); it.step(); hi = it.bound();
+}
+
+// main unit a as a piece [j_begin, j_begin + n_local) of its key steps; slot < 0: whole unit
+__device__ __forceinline__ UnitV1 skp_piece(const AttnParams& p, int a, int j_begin, int n_local, int slot) {
+  UnitV1 u = decode_unit(p, p.n_concept + a);
+  u.j_begin = j_begin; u.n_local = n_local; u.part_slot = slot; u.sk_unit = a;
+  return u;
+}
+
+// Calls f(unit) for every piece of CTA `first` in the order every role uses.
+template <typename F>
+__device__ __forceinline__ void v11p_for_each_piece(const AttnParams& p, int first, int stride, int total, F&& f) {
+  if (!p.skp_on) {
+#pragma unroll 1
+    for (int cta = first; cta < total; cta += stride) {
+      const UnitV1 u = decode_unit(p, cta);
+      if (u.n_local > 0) f(u);
+    }
+    return;
+  }
+#pragma unroll 1
+  for (int cta = first; cta < p.n_concept; cta += stride) {
+    const UnitV1 u = decode_unit(p, cta);
+    if (u.n_local > 0) f(u);
+  }
+  int64_t lo, hi;
+  skp_range(p, stride, first, lo, hi);
+  const int n = p.n_main_tiles;
+  bool is_first = true;
+#pragma unroll 1
+  while (lo < hi) {
+    const int a = (int)(lo / n), j0 = (int)(lo - (int64_t)a * n);
+    const int nl = (int)((hi - lo) < (int64_t)(n - j0) ? (hi - lo) : (int64_t)(n - j0));
+    const bool whole = j0 == 0 && nl == n;
+    f(skp_piece(p, a, j0, nl, whole ? -1 : 2 * first + (is_first ? 0 : 1)));
+    lo += nl;
+    is_first = false;
+  }
+}
 
 __device__ __forceinline__ void v11_producer(SmemV11& sm, const CUtensorMap* tmq, const CUtensorMap* tmk,
                                              const CUtensorMap* tmv, const UnitV1& u, int bh, V11Carry& c,
@@ -445,6 +522,80 @@ __device__ __forceinline__ void v11_mma(SmemV11& sm, uint32_t tmem, const UnitV1
   mma_commit(&sm.o_done);
   for (int t = 0; t < u.n_q; ++t) { c.steps[t] += n; ++c.units[t]; }
   ++c.n_units;
+}
+
+// Stream-K piece of a main unit (u.part_slot >= 0): leave (O unnormalised, row max, row sum) of tile t
+// in this piece's slot; the piece of (unit, tile) that arrives last merges all of them in range
+// order — fixed, so the result does not depend on who finishes last — and stores bf16.
+__device__ __forceinline__ void v11_partial_epilogue(SmemV11& sm, const AttnParams& p, const UnitV1& u, int t,
+                                                     int row, uint32_t t_o, float m_used, float l_sum,
+                                                     int b, int h, int q_row0, int q_rows) {
+  float* mine = p.ws_part + (size_t)u.part_slot * kPartFloats + t * kPartTile;
+  mine[kBM * kD + row] = m_used;
+  mine[kBM * kD + kBM + row] = l_sum;
+#pragma unroll
+  for (int c = 0; c < kD; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(t_o + c, r);
+    tmem_wait_ld32(r);
+#pragma unroll
+    for (int i = 0; i < 32; i += 4)
+      *reinterpret_cast<uint4*>(mine + (((c + i) >> 2) * kBM + row) * 4) =
+          make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);   // [col/4][row][4]: a warp stores 512 B runs
+  }
+  const int G = (int)gridDim.x, n = p.n_main_tiles;
+  const int64_t u_lo = (int64_t)u.sk_unit * n, u_hi = u_lo + n;
+  __threadfence();
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
+  if ((threadIdx.x & 127) == 0) {
+    int n_pieces = 0;
+    SkpIter it; it.init(p, G);
+    for (int i = 0; i < G; ++i) {
+      const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
+      if (lo >= u_hi) break;
+      if (hi > lo && hi > u_lo) ++n_pieces;
+    }
+    const int ticket = atomicAdd(p.ws_count + 2 * u.sk_unit + t, 1);
+    sm.sk_flag[t] = ticket == n_pieces - 1;
+  }
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
+  const bool last = sm.sk_flag[t] != 0;
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");   // the flag may be rewritten by the next piece
+  if (!last) return;
+  __threadfence();
+  const float scale = p.scale_log2;
+  float m_all = -INFINITY;
+  {
+    SkpIter it; it.init(p, G);
+    for (int i = 0; i < G; ++i) {
+      const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
+      if (lo >= u_hi) break;
+      if (!(hi > lo && hi > u_lo)) continue;
+      const float* pt = p.ws_part + (size_t)(2 * i + (lo >= u_lo ? 0 : 1)) * kPartFloats + t * kPartTile;
+      m_all = fmaxf(m_all, __ldcg(pt + kBM * kD + row));
+    }
+  }
+#pragma unroll 1
+  for (int c = 0; c < kD; c += 32) {
+    float acc[32], l_all = 0.f;
+#pragma unroll
+    for (int e = 0; e < 32; ++e) acc[e] = 0.f;
+    SkpIter it; it.init(p, G);
+    for (int i = 0; i < G; ++i) {
+      const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
+      if (lo >= u_hi) break;
+      if (!(hi > lo && hi > u_lo)) continue;
+      const float* pt = p.ws_part + (size_t)(2 * i + (lo >= u_lo ? 0 : 1)) * kPartFloats + t * kPartTile;
+      const float f = ex2((__ldcg(pt + kBM * kD + row) - m_all) * scale);
+      l_all += f * __ldcg(pt + kBM * kD + kBM + row);
+#pragma unroll
+      for (int e = 0; e < 32; e += 4) {
+        const float4 o4 = __ldcg(reinterpret_cast<const float4*>(pt + (((c + e) >> 2) * kBM + row) * 4));
+        acc[e] += f * o4.x; acc[e + 1] += f * o4.y; acc[e + 2] += f * o4.z; acc[e + 3] += f * o4.w;
+      }
+    }
+    if (row < q_rows) store_out_row(p, b, h, q_row0 + row, acc, 1.f / l_all, c, 32);
+  }
 }
 
 template <int kPolyEvery>
@@ -558,6 +709,10 @@ __device__ __forceinline__ void v11_softmax(SmemV11& sm, uint32_t tmem, const Un
 
   mbar_wait(&sm.o_done, unit0 & 1);
   tc_fence_after();
+  if (u.part_slot >= 0) {
+    v11_partial_epilogue(sm, p, u, t, row, t_o, m_used, l_sum, b, h, q_row0, q_rows);
+    return;
+  }
   const float inv_l = 1.f / l_sum;
 #pragma unroll
   for (int c = 0; c < kD; c += 32) {
@@ -640,6 +795,9 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
   SmemV11& sm = *reinterpret_cast<SmemV11*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int first = (int)blockIdx.x, stride = (int)gridDim.x;
+  // the very first loads go out before the CTA sync when the first piece is simply unit `first`
+  // (whole units, or a concept unit ahead of the key-step range)
+  const bool head_done = (!p.skp_on || first < p.n_concept) && decode_unit(p, first).n_local > 0;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
@@ -652,8 +810,10 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
     mbar_init(&sm.s_free, 4);
     mbar_init(&sm.o_done, 1);
     fence_barrier_init();
-    const UnitV1 u0 = decode_unit(p, first);
-    if (u0.n_local > 0) k2_first_loads<SmemV11, kV11Stages>(sm, &tmq, &tmk, u0, u0.bh);
+    if (head_done) {
+      const UnitV1 u0 = decode_unit(p, first);
+      k2_first_loads<SmemV11, kV11Stages>(sm, &tmq, &tmk, u0, u0.bh);
+    }
   }
   if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
   tc_fence_before();
@@ -666,37 +826,30 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
     if (warp == 0) {
       if (elect_one()) {
         V11Carry c;
-#pragma unroll 1
-        for (int cta = first; cta < total; cta += stride) {
-          const UnitV1 u = decode_unit(p, cta);
-          if (u.n_local > 0) v11_producer(sm, &tmq, &tmk, &tmv, u, u.bh, c, cta == first);
-        }
+        bool head = head_done;
+        v11p_for_each_piece(p, first, stride, total, [&](const UnitV1& u) {
+          v11_producer(sm, &tmq, &tmk, &tmv, u, u.bh, c, head);
+          head = false;
+        });
       }
     } else if (warp == 1) {
       if (elect_one()) {
         V11Carry c;
-#pragma unroll 1
-        for (int cta = first; cta < total; cta += stride) {
-          const UnitV1 u = decode_unit(p, cta);
-          if (u.n_local > 0) v11_mma(sm, tmem, u, c);
-        }
+        v11p_for_each_piece(p, first, stride, total, [&](const UnitV1& u) { v11_mma(sm, tmem, u, c); });
       }
     }
   } else {
     setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
     int step0 = 0, unit0 = 0;
-#pragma unroll 1
-    for (int cta = first; cta < total; cta += stride) {
-      const UnitV1 u = decode_unit(p, cta);
-      if (u.n_local == 0) continue;
+    v11p_for_each_piece(p, first, stride, total, [&](const UnitV1& u) {
       if (t < u.n_q) {
         const int b = u.bh / p.H, h = u.bh - b * p.H;
         v11_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h, step0, unit0);
         step0 += u.n_local;
       }
       ++unit0;
-    }
+    });
   }
   tc_fence_before();
   __syncthreads();

@@ -192,7 +192,6 @@ def test_joint_attention_stream_k_tail(ops, B, H, P, T, C, sms):
     q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((30, 1.5), (31, 1.0), (32, 1.0)))
     V3 = _cabi.K2_V3                                   # the kernel with the stream-K tail, chosen per call
     assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, 0, V3, -1) == 0
-    assert lib.ca_joint_attention_workspace_bytes(B, H, P, T, C, 0) == 0      # default kernels never split
     base = ops.joint_attention(q, k, v, P, T, C, impl=V3, plan_sms=-1)
     assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, 0, V3, sms) > 0, "plan did not split: pick other sizes"
     runs = [ops.joint_attention(q, k, v, P, T, C, impl=V3, plan_sms=sms) for _ in range(3)]
@@ -226,6 +225,38 @@ def test_joint_attention_every_kernel_matches_oracle(ops, impl, B, H, P, T, C, m
         if P:
             close(oi, ri, rtol=2e-2, atol=1e-2)
         close(ot, rt, rtol=2e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("B,H,P,T,C,mode", [(1, 8, 2048, 128, 3, 0), (1, 24, 4096, 512, 20, 0), (2, 6, 1300, 200, 5, 1),
+                                            (1, 3, 16384, 256, 32, 0)])
+def test_joint_attention_persistent_key_step_ranges(ops, B, H, P, T, C, mode):
+    """CA_K2_V11P with stream-K on (the default for these shapes): every CTA works on an equal share
+    of the key steps, units cut by a share boundary are merged in fp32 by the piece that finishes
+    last.  Must match the one-unit-per-CTA kernel to a bf16 ulp (fp32 merge vs in-TMEM accumulation),
+    the oracle like every kernel, and be REPRODUCIBLE bit for bit (fixed merge order); plan_sms < 0
+    turns the ranges off (whole units, no workspace)."""
+    from conceptattention_b200 import _cabi
+    lib = _cabi.load()
+    N = P + T + C
+    q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((60, 1.5), (61, 1.0), (62, 1.0)))
+    V11P, V11 = _cabi.K2_V11P, _cabi.K2_V11
+    assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, V11P, 0) > 0, "ranges not planned: pick other sizes"
+    assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, V11P, -1) == 0
+    base = ops.joint_attention(q, k, v, P, T, C, mode, impl=V11)
+    whole = ops.joint_attention(q, k, v, P, T, C, mode, impl=V11P, plan_sms=-1)
+    runs = [ops.joint_attention(q, k, v, P, T, C, mode, impl=V11P) for _ in range(3)]
+    auto = ops.joint_attention(q, k, v, P, T, C, mode)
+    torch.cuda.synchronize()
+    for got, b, w in zip(runs[0], base, whole):
+        assert torch.equal(b, w)                            # same per-unit maths without the ranges
+        close(got, b, rtol=8e-3, atol=2e-3)
+    for r in runs[1:]:
+        assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1])
+    if P <= 4096 and H <= 8:
+        ri, rt = _attention_oracle(q.float().cpu(), k.float().cpu(), v.float().cpu(), P, T, C, mode)
+        close(runs[0][0], ri, rtol=2e-2, atol=1e-2)
+        close(runs[0][1], rt, rtol=2e-2, atol=1e-2)
+    assert auto[0].shape == runs[0][0].shape
 
 
 def test_joint_attention_one_way(ops):
