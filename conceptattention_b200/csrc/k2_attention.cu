@@ -740,7 +740,8 @@ static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode) {
   pl.W = W; pl.G = sms; pl.wc = (2 * nc + 2) / 3;          // one tile per step instead of two: ~2/3 of the cost
   const int64_t T_cost = W * n + n_concept * pl.wc;
   const int64_t whole = ((W + n_concept + sms - 1) / sms) * n;
-  pl.on = W * n >= (int64_t)8 * sms && whole * sms * 100 >= T_cost * 108 && W * n < 0x7fffffffLL;
+  // (a CTA's share is at least 8 key steps and a unit has at most 16 pieces: W >= sms / 14)
+  pl.on = W * n >= (int64_t)8 * sms && W * 14 >= sms && whole * sms * 100 >= T_cost * 108 && W * n < 0x7fffffffLL;
   return pl;
 }
 static size_t skp_workspace_bytes(const SkpPlan& pl) {

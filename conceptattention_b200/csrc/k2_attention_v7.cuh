@@ -340,6 +340,7 @@ struct SmemV11 {
   uint64_t q_empty[2];                                      // persistent form only
   uint32_t tmem_base;
   int sk_flag[2];                                           // stream-K: "this piece merges" per tile
+  int sk_n[2], sk_list[2][16];                              // slots of the pieces of the unit being merged
 };
 
 // Phase counters that run on from unit to unit in the persistent form (all zero for a
@@ -362,24 +363,28 @@ struct V11Carry {
 // row sum) per tile in its CTA's slot and the piece that finishes last merges — v3's fix-up, with
 // the pieces of one range run back to back by ONE CTA.
 struct SkpIter {                                          // incremental B(i), i = 0, 1, 2, ...
-  int64_t T, Sm, conc, best;
+  int64_t Sm, conc, best, quo;                              // quo = floor(i * T / G), rem = (i * T) % G
+  int64_t tq; int tr, rem;                                  // T = tq * G + tr
   int i, G, n_concept, wc;
   __device__ __forceinline__ void init(const AttnParams& p, int G_) {
     G = G_; n_concept = p.n_concept; wc = p.skp_wc;
     Sm = (int64_t)p.n_dp * p.n_main_tiles;
-    T = Sm + (int64_t)n_concept * wc;
-    conc = 0; best = 0; i = 0;
+    const int64_t T = Sm + (int64_t)n_concept * wc;
+    tq = T / G; tr = (int)(T - tq * G);                     // the only division
+    conc = 0; best = 0; quo = 0; rem = 0; i = 0;
   }
   __device__ __forceinline__ int64_t bound() const {       // B(i)
     if (i >= G) return Sm;
-    const int64_t v = (int64_t)i * T / G - conc;
+    const int64_t v = quo - conc;
     const int64_t b = v > best ? v : best;
     return b < Sm ? b : Sm;
   }
   __device__ __forceinline__ void step() {                 // i -> i + 1
-    const int64_t v = (int64_t)i * T / G - conc;
+    const int64_t v = quo - conc;
     if (v > best) best = v;
     if (i < n_concept) conc += (int64_t)((n_concept - i + G - 1) / G) * wc;
+    quo += tq; rem += tr;
+    if (rem >= G) { rem -= G; ++quo; }
     ++i;
   }
 };
@@ -548,44 +553,44 @@ __device__ __forceinline__ void v11_partial_epilogue(SmemV11& sm, const AttnPara
   __threadfence();
   asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
   if ((threadIdx.x & 127) == 0) {
+    // the pieces of this unit, in range order: CTA i holds one iff its range meets [u_lo, u_hi);
+    // it is CTA i's first piece (slot 2i) when the range starts inside the unit, else its last (2i+1)
     int n_pieces = 0;
     SkpIter it; it.init(p, G);
     for (int i = 0; i < G; ++i) {
       const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
       if (lo >= u_hi) break;
-      if (hi > lo && hi > u_lo) ++n_pieces;
+      if (hi > lo && hi > u_lo) {
+        if (n_pieces < 16) sm.sk_list[t][n_pieces] = 2 * i + (lo >= u_lo ? 0 : 1);
+        ++n_pieces;
+      }
     }
+    sm.sk_n[t] = n_pieces;
     const int ticket = atomicAdd(p.ws_count + 2 * u.sk_unit + t, 1);
     sm.sk_flag[t] = ticket == n_pieces - 1;
   }
   asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
   const bool last = sm.sk_flag[t] != 0;
+  const int n_pieces = sm.sk_n[t];
   asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");   // the flag may be rewritten by the next piece
-  if (!last) return;
+  if (!last) return;                                            // (the list only after this warpgroup's next barrier)
+  const int* slots = sm.sk_list[t];
   __threadfence();
   const float scale = p.scale_log2;
   float m_all = -INFINITY;
-  {
-    SkpIter it; it.init(p, G);
-    for (int i = 0; i < G; ++i) {
-      const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
-      if (lo >= u_hi) break;
-      if (!(hi > lo && hi > u_lo)) continue;
-      const float* pt = p.ws_part + (size_t)(2 * i + (lo >= u_lo ? 0 : 1)) * kPartFloats + t * kPartTile;
-      m_all = fmaxf(m_all, __ldcg(pt + kBM * kD + row));
-    }
+#pragma unroll 1
+  for (int i = 0; i < n_pieces; ++i) {
+    const float* pt = p.ws_part + (size_t)slots[i] * kPartFloats + t * kPartTile;
+    m_all = fmaxf(m_all, __ldcg(pt + kBM * kD + row));
   }
 #pragma unroll 1
   for (int c = 0; c < kD; c += 32) {
     float acc[32], l_all = 0.f;
 #pragma unroll
     for (int e = 0; e < 32; ++e) acc[e] = 0.f;
-    SkpIter it; it.init(p, G);
-    for (int i = 0; i < G; ++i) {
-      const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
-      if (lo >= u_hi) break;
-      if (!(hi > lo && hi > u_lo)) continue;
-      const float* pt = p.ws_part + (size_t)(2 * i + (lo >= u_lo ? 0 : 1)) * kPartFloats + t * kPartTile;
+#pragma unroll 1
+    for (int i = 0; i < n_pieces; ++i) {
+      const float* pt = p.ws_part + (size_t)slots[i] * kPartFloats + t * kPartTile;
       const float f = ex2((__ldcg(pt + kBM * kD + row) - m_all) * scale);
       l_all += f * __ldcg(pt + kBM * kD + kBM + row);
 #pragma unroll
