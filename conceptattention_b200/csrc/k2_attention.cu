@@ -741,7 +741,11 @@ static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode) {
   const int64_t T_cost = W * n + n_concept * pl.wc;
   const int64_t whole = ((W + n_concept + sms - 1) / sms) * n;
   // (a CTA's share is at least 8 key steps and a unit has at most 16 pieces: W >= sms / 14)
-  pl.on = W * n >= (int64_t)8 * sms && W * 14 >= sms && whole * sms * 100 >= T_cost * 108 && W * n < 0x7fffffffLL;
+  // Measured (scripts/bench_attention.py): with fewer than two waves of units the ranges win big
+  // (3 heads x 16.6K rows: 0.34 ms against 0.39-0.45); with ~3 or more units per CTA every CTA pays two
+  // partial pieces + a merge for a few per cent of balance and loses (config 2: 0.244 vs 0.183 ms).
+  pl.on = W * n >= (int64_t)8 * sms && W * 14 >= sms && W + n_concept < 2 * (int64_t)sms &&
+          whole * sms * 100 >= T_cost * 108 && W * n < 0x7fffffffLL;
   return pl;
 }
 static size_t skp_workspace_bytes(const SkpPlan& pl) {
