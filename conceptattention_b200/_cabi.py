@@ -34,6 +34,7 @@ SIGNATURES = {
     "ca_joint_attention_ws": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, C.c_size_t, _p],
     "ca_joint_attention_workspace_bytes_ex": [_i] * 8,
     "ca_joint_attention_ex": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, C.c_size_t, _i, _i, _p],
+    "ca_joint_attention_noalloc": [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _i, _i, _p],
     "ca_heatmap_accumulate": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p],
     "ca_heatmap_accumulate_pair": [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _p,
                                    _i64, _p, _i, _p],

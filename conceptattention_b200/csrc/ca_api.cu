@@ -16,6 +16,7 @@ extern "C" const char* ca_status_string(ca_status s) {
     case CA_ERR_ALIGNMENT: return "pointer or stride not 16-byte aligned";
     case CA_ERR_ARCH: return "device is not sm_100 (B200)";
     case CA_ERR_CUDA: return "CUDA error (see ca_last_cuda_error)";
+    case CA_ERR_SCRATCH_LIMIT: return "scratch need exceeds the static no-alloc array (CA_K2_NOALLOC_MAX_BYTES)";
     default: return "unknown status";
   }
 }

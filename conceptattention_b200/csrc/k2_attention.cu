@@ -889,3 +889,30 @@ extern "C" ca_status ca_joint_attention(const void* q, const void* k, const void
                                         void* out_txtc, void* stream) {
   return ca_joint_attention_ex(q, k, v, B, H, P, T, C, mode, out_img, out_txtc, nullptr, 0, CA_K2_AUTO, 0, stream);
 }
+
+// ---- no-allocation variant (see include/conceptattention_b200.h) -------------
+// The scratch of the tail balancing lives in a file-scope device array.  In host code its name is
+// only a stand-in: the device address comes from cudaGetSymbolAddress, once per device, with that
+// device current.  Shared by every call on the device; the callee clears the arrival counters on
+// the stream at the start of each call.
+static __device__ __align__(256) unsigned char g_k2_noalloc_scratch[CA_K2_NOALLOC_MAX_BYTES];
+
+extern "C" ca_status ca_joint_attention_noalloc(const void* q, const void* k, const void* v, int B, int H,
+                                                int P, int T, int C, int mode, void* out_img,
+                                                void* out_txtc, int impl, int plan_sms, void* stream) {
+  constexpr int kMaxDevices = 64;
+  static void* scratch_of[kMaxDevices] = {};
+  if (B < 0 || H <= 0 || P < 0 || T < 0 || C < 0) return CA_ERR_INVALID_ARG;
+  const size_t need = ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, impl, plan_sms);
+  if (need > (size_t)CA_K2_NOALLOC_MAX_BYTES) return CA_ERR_SCRATCH_LIMIT;
+  int dev = 0;
+  CA_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return CA_ERR_UNSUPPORTED;
+  if (!scratch_of[dev]) {
+    void* ptr = nullptr;
+    CA_CUDA_OK(cudaGetSymbolAddress(&ptr, g_k2_noalloc_scratch));
+    scratch_of[dev] = ptr;
+  }
+  return ca_joint_attention_ex(q, k, v, B, H, P, T, C, mode, out_img, out_txtc, scratch_of[dev],
+                               (size_t)CA_K2_NOALLOC_MAX_BYTES, impl, plan_sms, stream);
+}

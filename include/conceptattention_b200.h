@@ -38,7 +38,8 @@ enum {
   CA_ERR_UNSUPPORTED = -2,   /* shape outside what the kernels are built for    */
   CA_ERR_ALIGNMENT = -3,     /* pointer / stride not 16-byte aligned            */
   CA_ERR_ARCH = -4,          /* device is not sm_100                            */
-  CA_ERR_CUDA = -5           /* CUDA runtime/driver error; see ca_last_cuda_error */
+  CA_ERR_CUDA = -5,          /* CUDA runtime/driver error; see ca_last_cuda_error */
+  CA_ERR_SCRATCH_LIMIT = -6  /* the call needs more scratch than the static no-alloc array holds */
 };
 
 #define CA_HEAD_DIM 128      /* Flux head dim (hidden 3072 / 24 heads)           */
@@ -153,6 +154,26 @@ ca_status ca_joint_attention_ex(const void* q, const void* k, const void* v,
                                 void* out_img, void* out_txtc,
                                 void* workspace, size_t workspace_bytes,
                                 int impl, int plan_sms, void* stream);
+
+/* ---- K2 without any allocation by anybody -------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  ca_joint_attention_ex with the scratch of its tail balancing (the stream-K partials of
+ * CA_K2_V3 and the key-step ranges of CA_K2_V11P) taken from ONE file-scope static __device__ array of
+ * CA_K2_NOALLOC_MAX_BYTES (40 MiB, held by every GPU that loads the library until exit) instead of
+ * a caller-owned workspace.  The entry point calls no cudaMalloc / cudaFree / allocating library
+ * routine; inputs and outputs are still the caller's.  A call whose plan needs more scratch than
+ * the array holds is rejected with CA_ERR_SCRATCH_LIMIT before anything is launched
+ * (ca_joint_attention_workspace_bytes_ex tells the need in advance; plan_sms < 0 never needs any).
+ * Every call on a device shares the array: the arrival counters are cleared on the stream at the
+ * start of each call, the partials are overwritten before they are read, but two calls that
+ * overlap on the GPU (different streams, or graphs replayed concurrently) RACE on it — serialise
+ * them.  Results are identical to ca_joint_attention_ex with a caller workspace. */
+#define CA_K2_NOALLOC_MAX_BYTES (40u << 20)
+ca_status ca_joint_attention_noalloc(const void* q, const void* k, const void* v,
+                                     int B, int H, int P, int T, int C, int mode,
+                                     void* out_img, void* out_txtc,
+                                     int impl, int plan_sms, void* stream);
 
 /* ---- K3+K4: heatmap logits + normalise over concepts + accumulate -----------
  * logits[b,c,p] = sum_{s<nseg} sum_{j<seg_len} img[b,s,p,j] * con[b,s,c,j]
