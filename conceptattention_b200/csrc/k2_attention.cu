@@ -699,18 +699,6 @@ extern "C" int ca_debug_streamk_piece(int n_steps, int sk_units, int sk_sms, int
   return ok ? 1 : 0;
 }
 
-// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO, measured on B200 (148 SMs;
-// three alternating runs of 60 launches each, profiles/r02_k2_variants.md): the persistent form of v11
-// up to 64 key steps per query-tile unit (config 2 +2 %, config 4 +6 %, config 3 +8 % over the
-// one-unit-per-CTA v11) and for longer units when there are fewer than two waves of them (3 heads x
-// 16.6K rows: 0.41-0.45 ms against 0.45-0.53 for v7); v7 for long units in many waves (config 5 on one
-// or two GPUs: 2-5 % ahead of v11p).
-static int resolve_impl(int impl, int n_steps, int64_t units = 0) {
-  if (impl != CA_K2_AUTO) return impl;
-  if (n_steps <= 64) return CA_K2_V11P;
-  return units < 2 * 148 ? CA_K2_V11P : CA_K2_V7;
-}
-
 namespace ca {
 static int sm_count_cached() {
   static int n = 0;
@@ -724,9 +712,14 @@ static int sm_count_cached() {
 }
 // Key-step ranges for the persistent v11 (see SkpIter): on when whole units would leave the last
 // wave at least 8 % longer than an even split of the work, and a CTA's share is at least 8 key steps.
-struct SkpPlan { bool on; int G, wc; int64_t W; };
-static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode) {
-  SkpPlan pl{false, 0, 0, 0};
+// Persistent v11 with a balanced tail: the flat list [concept | main] is run in whole waves of G
+// CTAs in lockstep (static stride: the CTAs of a wave work on neighbouring heads, which keeps their
+// K/V in L2) and only the R main units left over at the end are cut into key-step ranges (SkpIter).
+// n_dp = main units run whole, R = tail units.  When the tail is tiny (a unit would be cut into more
+// than 14 pieces) one whole wave is added to it.
+struct SkpPlan { bool on; int G, wc; int64_t n_dp, R; };
+static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode, bool force = false) {
+  SkpPlan pl{false, 0, 0, 0, 0};
   const int sms = sm_count_cached();
   if (sms <= 0 || B <= 0 || H <= 0 || P + T <= 0) return pl;
   const int n = (P + T + kBM - 1) / kBM;
@@ -737,30 +730,48 @@ static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode) {
     if (mode != CA_ATTN_SELF_ONLY) nc += (P + kBN - 1) / kBN;
     if (mode != CA_ATTN_CROSS_ONLY) nc += (C + kBN - 1) / kBN;
   }
-  pl.W = W; pl.G = sms; pl.wc = (2 * nc + 2) / 3;          // one tile per step instead of two: ~2/3 of the cost
+  pl.G = sms; pl.wc = (2 * nc + 2) / 3;                    // one tile per step instead of two: ~2/3 of the cost
+  const int64_t E = W + n_concept;
+  int64_t e_whole = (E / sms) * sms;                       // entries of the flat list run in whole waves
+  if ((E - e_whole) * 14 < sms && e_whole >= sms) e_whole -= sms;
+  if (e_whole < n_concept) e_whole = n_concept;            // concept units are never cut
+  pl.n_dp = e_whole - n_concept;
+  pl.R = W - pl.n_dp;
   const int64_t T_cost = W * n + n_concept * pl.wc;
-  const int64_t whole = ((W + n_concept + sms - 1) / sms) * n;
-  // (a CTA's share is at least 8 key steps and a unit has at most 16 pieces: W >= sms / 14)
-  // Measured (scripts/bench_attention.py): with fewer than two waves of units the ranges win big
-  // (3 heads x 16.6K rows: 0.34 ms against 0.39-0.45); with ~3 or more units per CTA every CTA pays two
-  // partial pieces + a merge for a few per cent of balance and loses (config 2: 0.244 vs 0.183 ms).
-  pl.on = W * n >= (int64_t)8 * sms && W * 14 >= sms && W + n_concept < 2 * (int64_t)sms &&
-          whole * sms * 100 >= T_cost * 108 && W * n < 0x7fffffffLL;
+  const int64_t whole = ((E + sms - 1) / sms) * n;          // time of the launch without ranges, in key steps
+  // structural limits: table size, tail share of at least 8 key steps per CTA, at most ~14 pieces per unit
+  pl.on = sms <= kSkpMaxCtas && pl.R > 0 && pl.R * n >= (int64_t)8 * sms && pl.R * 14 >= sms &&
+          pl.R * n < 0x7fffffffLL;
+  // measured rule (skipped when forced by plan_sms > 0; profiles/r02_k2_variants.md): the launch without
+  // ranges is at least 6 % longer than an even split
+  if (pl.on && !force) pl.on = whole * sms * 100 >= T_cost * 106;
   return pl;
 }
 static size_t skp_workspace_bytes(const SkpPlan& pl) {
-  return (size_t)2 * pl.G * kPartFloats * sizeof(float) + (size_t)2 * pl.W * sizeof(int) + 256;
+  return (size_t)2 * pl.G * kPartFloats * sizeof(float) + (size_t)2 * pl.R * sizeof(int) + 256;
 }
 }  // namespace ca
+
+// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO, measured on B200 (148 SMs;
+// alternating single-shape runs of 60 launches, profiles/r02_k2_variants.md): the persistent v11 up to
+// 64 key steps per query-tile unit (config 2 +2 %, config 3 +8 %, config 4 +6 % over one unit per CTA)
+// and for longer units whenever its balanced tail is planned (config 5: 24 heads 2.64 vs 2.70 ms for
+// v7, 12 heads 1.26 vs 1.36, 3 heads 0.32 vs 0.45); v7 for long units in well-filled waves.
+static int resolve_impl(int impl, int B, int H, int P, int T, int C, int mode) {
+  if (impl != CA_K2_AUTO) return impl;
+  const int n_steps = (P + T + ca::kBM - 1) / ca::kBM;
+  if (n_steps <= 64) return CA_K2_V11P;
+  return ca::plan_v11p(B, H, P, T, C, mode).on ? CA_K2_V11P : CA_K2_V7;
+}
 
 extern "C" size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,
                                                         int impl, int plan_sms) {
   using namespace ca;
   if (B <= 0 || H <= 0 || P + T <= 0) return 0;
   const int n_main = (P + T + kBM - 1) / kBM;
-  const int which = resolve_impl(impl, n_main, (int64_t)((n_main + 1) / 2) * B * H);
+  const int which = resolve_impl(impl, B, H, P, T, C, mode);
   if (which == CA_K2_V11P && plan_sms >= 0) {                 // key-step ranges of the persistent kernel
-    const SkpPlan sp = plan_v11p(B, H, P, T, C, mode);
+    const SkpPlan sp = plan_v11p(B, H, P, T, C, mode, plan_sms > 0);
     return sp.on ? skp_workspace_bytes(sp) : 0;
   }
   if (which != CA_K2_V3) return 0;
@@ -825,7 +836,7 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   if ((s = make_qkv_tmap(&tmv, v, B * H, Ntot, kBN)) != CA_OK) return s;
 
   const bool concept_attn = C > 0 && mode != CA_ATTN_NEITHER;
-  const int kernel = resolve_impl(impl, p.n_main_tiles, (int64_t)p.n_pairs * B * H);
+  const int kernel = resolve_impl(impl, B, H, P, T, C, mode);
   const int W = p.n_pairs * B * H;
   p.n_concept = concept_attn ? B * H : 0;
   const size_t need = ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, impl, plan_sms);
@@ -843,12 +854,13 @@ extern "C" ca_status ca_joint_attention_ex(const void* q, const void* k, const v
   if (ctas > 0) {
     // every kernel: polynomial exp2 on every 4th element pair (the MUFU / FMA-pipe balance point)
     if (kernel == CA_K2_V11P) {
-      const SkpPlan sp = plan_v11p(B, H, P, T, C, mode);
+      const SkpPlan sp = plan_v11p(B, H, P, T, C, mode, plan_sms > 0);
       if (sp.on && plan_sms >= 0 && workspace != nullptr && workspace_bytes >= skp_workspace_bytes(sp)) {
         p.skp_on = 1; p.skp_wc = sp.wc;
+        p.n_dp = (int)sp.n_dp; p.sk_units = (int)sp.R;
         p.ws_part = (float*)workspace;
         p.ws_count = (int*)((char*)workspace + (size_t)2 * sp.G * kPartFloats * sizeof(float));
-        CA_CUDA_OK(cudaMemsetAsync(p.ws_count, 0, (size_t)2 * sp.W * sizeof(int), st));
+        CA_CUDA_OK(cudaMemsetAsync(p.ws_count, 0, (size_t)2 * sp.R * sizeof(int), st));
       }
       static bool configured = false;
       static int sms = 0;

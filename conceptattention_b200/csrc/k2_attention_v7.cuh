@@ -331,6 +331,7 @@ attn_v7_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ 
 // The k-th QK of the CTA waits for phase k-1 of the single s_free barrier.
 // =============================================================================
 constexpr int kV11Stages = 5;
+constexpr int kSkpMaxCtas = 256;                         // persistent CTAs the key-step ranges are planned for (<= SMs)
 
 struct SmemV11 {
   uint8_t q[2][kTileBytes];
@@ -341,6 +342,7 @@ struct SmemV11 {
   uint32_t tmem_base;
   int sk_flag[2];                                           // stream-K: "this piece merges" per tile
   int sk_n[2], sk_list[2][16];                              // slots of the pieces of the unit being merged
+  int skp_bound[kSkpMaxCtas + 1];                           // stream-K: CTA i works on key steps [bound[i], bound[i+1])
 };
 
 // Phase counters that run on from unit to unit in the persistent form (all zero for a
@@ -365,12 +367,21 @@ struct V11Carry {
 struct SkpIter {                                          // incremental B(i), i = 0, 1, 2, ...
   int64_t Sm, conc, best, quo;                              // quo = floor(i * T / G), rem = (i * T) % G
   int64_t tq; int tr, rem;                                  // T = tq * G + tr
-  int i, G, n_concept, wc;
+  int i, G, n_concept, n_whole, wc, n;
+  // cost of the WHOLE entries of CTA i (flat list [concept | main], entries i, i + G, ... below n_whole)
+  __device__ __forceinline__ int64_t whole_cost(int c) const {
+    if (c >= n_whole) return 0;
+    const int cnt = (n_whole - c + G - 1) / G;
+    const int ccn = c < n_concept ? (n_concept - c + G - 1) / G : 0;
+    return (int64_t)ccn * wc + (int64_t)(cnt - ccn) * n;
+  }
   __device__ __forceinline__ void init(const AttnParams& p, int G_) {
-    G = G_; n_concept = p.n_concept; wc = p.skp_wc;
-    Sm = (int64_t)p.n_dp * p.n_main_tiles;
-    const int64_t T = Sm + (int64_t)n_concept * wc;
-    tq = T / G; tr = (int)(T - tq * G);                     // the only division
+    G = G_; n_concept = p.n_concept; wc = p.skp_wc; n = p.n_main_tiles;
+    n_whole = p.n_concept + p.n_dp;
+    Sm = (int64_t)p.sk_units * n;                           // key steps of the tail units
+    // total cost: every concept unit wc, every whole main unit n, plus the tail
+    const int64_t T = Sm + (int64_t)n_concept * wc + (int64_t)p.n_dp * n;
+    tq = T / G; tr = (int)(T - tq * G);                     // the only 64-bit division
     conc = 0; best = 0; quo = 0; rem = 0; i = 0;
   }
   __device__ __forceinline__ int64_t bound() const {       // B(i)
@@ -382,29 +393,27 @@ struct SkpIter {                                          // incremental B(i), i
   __device__ __forceinline__ void step() {                 // i -> i + 1
     const int64_t v = quo - conc;
     if (v > best) best = v;
-    if (i < n_concept) conc += (int64_t)((n_concept - i + G - 1) / G) * wc;
+    conc += whole_cost(i);
     quo += tq; rem += tr;
     if (rem >= G) { rem -= G; ++quo; }
     ++i;
   }
 };
 
-__device__ __forceinline__ void skp_range(const AttnParams& p, int G, int c, int64_t& lo, int64_t& hi) {
-  SkpIter it; it.init(p, G);
-  for (int k = 0; k < c; ++k) it.step();
-  lo = it.bound(); it.step(); hi = it.bound();
-}
-
-// main unit a as a piece [j_begin, j_begin + n_local) of its key steps; slot < 0: whole unit
+// tail unit a (0 <= a < sk_units; main unit n_dp + a) as a piece [j_begin, j_begin + n_local) of its
+// key steps; slot < 0: the whole unit
 __device__ __forceinline__ UnitV1 skp_piece(const AttnParams& p, int a, int j_begin, int n_local, int slot) {
-  UnitV1 u = decode_unit(p, p.n_concept + a);
+  AttnParams q = p;
+  q.n_dp = 0x7fffffff;                                     // decode as a plain main unit
+  UnitV1 u = decode_unit(q, p.n_concept + p.n_dp + a);
   u.j_begin = j_begin; u.n_local = n_local; u.part_slot = slot; u.sk_unit = a;
   return u;
 }
 
 // Calls f(unit) for every piece of CTA `first` in the order every role uses.
 template <typename F>
-__device__ __forceinline__ void v11p_for_each_piece(const AttnParams& p, int first, int stride, int total, F&& f) {
+__device__ __forceinline__ void v11p_for_each_piece(const AttnParams& p, const int* bound, int first, int stride,
+                                                    int total, F&& f) {
   if (!p.skp_on) {
 #pragma unroll 1
     for (int cta = first; cta < total; cta += stride) {
@@ -414,12 +423,11 @@ __device__ __forceinline__ void v11p_for_each_piece(const AttnParams& p, int fir
     return;
   }
 #pragma unroll 1
-  for (int cta = first; cta < p.n_concept; cta += stride) {
+  for (int cta = first; cta < p.n_concept + p.n_dp; cta += stride) {   // whole entries, in lockstep with the other CTAs
     const UnitV1 u = decode_unit(p, cta);
     if (u.n_local > 0) f(u);
   }
-  int64_t lo, hi;
-  skp_range(p, stride, first, lo, hi);
+  int64_t lo = bound[first], hi = bound[first + 1];         // table built once per CTA in the prologue
   const int n = p.n_main_tiles;
   bool is_first = true;
 #pragma unroll 1
@@ -556,12 +564,12 @@ __device__ __forceinline__ void v11_partial_epilogue(SmemV11& sm, const AttnPara
     // the pieces of this unit, in range order: CTA i holds one iff its range meets [u_lo, u_hi);
     // it is CTA i's first piece (slot 2i) when the range starts inside the unit, else its last (2i+1)
     int n_pieces = 0;
-    SkpIter it; it.init(p, G);
-    for (int i = 0; i < G; ++i) {
-      const int64_t lo = it.bound(); it.step(); const int64_t hi = it.bound();
-      if (lo >= u_hi) break;
-      if (hi > lo && hi > u_lo) {
-        if (n_pieces < 16) sm.sk_list[t][n_pieces] = 2 * i + (lo >= u_lo ? 0 : 1);
+    const int* bnd = sm.skp_bound;
+    int i0 = (int)blockIdx.x;
+    while (i0 > 0 && bnd[i0] > u_lo) --i0;                // first CTA whose range reaches into the unit
+    for (int i = i0; i < G && bnd[i] < u_hi; ++i) {
+      if (bnd[i + 1] > bnd[i] && bnd[i + 1] > u_lo) {
+        if (n_pieces < 16) sm.sk_list[t][n_pieces] = 2 * i + (bnd[i] >= u_lo ? 0 : 1);
         ++n_pieces;
       }
     }
@@ -584,22 +592,26 @@ __device__ __forceinline__ void v11_partial_epilogue(SmemV11& sm, const AttnPara
     m_all = fmaxf(m_all, __ldcg(pt + kBM * kD + row));
   }
 #pragma unroll 1
-  for (int c = 0; c < kD; c += 32) {
-    float acc[32], l_all = 0.f;
+  for (int c = 0; c < kD; c += 64) {                        // 16 x 16-byte loads in flight per piece
+    float acc[64], l_all = 0.f;
 #pragma unroll
-    for (int e = 0; e < 32; ++e) acc[e] = 0.f;
+    for (int e = 0; e < 64; ++e) acc[e] = 0.f;
 #pragma unroll 1
     for (int i = 0; i < n_pieces; ++i) {
       const float* pt = p.ws_part + (size_t)slots[i] * kPartFloats + t * kPartTile;
+      float4 o4[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e)
+        o4[e] = __ldcg(reinterpret_cast<const float4*>(pt + (((c >> 2) + e) * kBM + row) * 4));
       const float f = ex2((__ldcg(pt + kBM * kD + row) - m_all) * scale);
       l_all += f * __ldcg(pt + kBM * kD + kBM + row);
 #pragma unroll
-      for (int e = 0; e < 32; e += 4) {
-        const float4 o4 = __ldcg(reinterpret_cast<const float4*>(pt + (((c + e) >> 2) * kBM + row) * 4));
-        acc[e] += f * o4.x; acc[e + 1] += f * o4.y; acc[e + 2] += f * o4.z; acc[e + 3] += f * o4.w;
+      for (int e = 0; e < 16; ++e) {
+        acc[4 * e] += f * o4[e].x; acc[4 * e + 1] += f * o4[e].y;
+        acc[4 * e + 2] += f * o4[e].z; acc[4 * e + 3] += f * o4[e].w;
       }
     }
-    if (row < q_rows) store_out_row(p, b, h, q_row0 + row, acc, 1.f / l_all, c, 32);
+    if (row < q_rows) store_out_row(p, b, h, q_row0 + row, acc, 1.f / l_all, c, 64);
   }
 }
 
@@ -802,7 +814,7 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
   const int first = (int)blockIdx.x, stride = (int)gridDim.x;
   // the very first loads go out before the CTA sync when the first piece is simply unit `first`
   // (whole units, or a concept unit ahead of the key-step range)
-  const bool head_done = (!p.skp_on || first < p.n_concept) && decode_unit(p, first).n_local > 0;
+  const bool head_done = (!p.skp_on || first < p.n_concept + p.n_dp) && decode_unit(p, first).n_local > 0;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmq); prefetch_tmap(&tmk); prefetch_tmap(&tmv);
@@ -821,6 +833,10 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
     }
   }
   if (warp == 2) { tmem_alloc(&sm.tmem_base, 512); tmem_relinquish(); }
+  if (p.skp_on && threadIdx.x == 96) {                      // idle warp 3: the range table, once per CTA
+    SkpIter it; it.init(p, stride);
+    for (int i = 0; i <= stride; ++i) { sm.skp_bound[i] = (int)it.bound(); it.step(); }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -832,7 +848,7 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
       if (elect_one()) {
         V11Carry c;
         bool head = head_done;
-        v11p_for_each_piece(p, first, stride, total, [&](const UnitV1& u) {
+        v11p_for_each_piece(p, sm.skp_bound, first, stride, total, [&](const UnitV1& u) {
           v11_producer(sm, &tmq, &tmk, &tmv, u, u.bh, c, head);
           head = false;
         });
@@ -840,14 +856,14 @@ attn_v11p_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant_
     } else if (warp == 1) {
       if (elect_one()) {
         V11Carry c;
-        v11p_for_each_piece(p, first, stride, total, [&](const UnitV1& u) { v11_mma(sm, tmem, u, c); });
+        v11p_for_each_piece(p, sm.skp_bound, first, stride, total, [&](const UnitV1& u) { v11_mma(sm, tmem, u, c); });
       }
     }
   } else {
     setmaxnreg_inc<200>();
     const int t = (warp >> 2) - 1;
     int step0 = 0, unit0 = 0;
-    v11p_for_each_piece(p, first, stride, total, [&](const UnitV1& u) {
+    v11p_for_each_piece(p, sm.skp_bound, first, stride, total, [&](const UnitV1& u) {
       if (t < u.n_q) {
         const int b = u.bh / p.H, h = u.bh - b * p.H;
         v11_softmax<kPolyEvery>(sm, tmem, u, p, t, b, h, step0, unit0);

@@ -135,16 +135,21 @@ ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v,
 
 /* Same, with the kernel and the tail plan chosen PER CALL (no process-wide switches):
  *   impl     CA_K2_AUTO  the default of the two calls above (measured on B200): CA_K2_V11P for units of
- *                        up to 64 key steps and for longer units in fewer than two waves of the SMs,
- *                        CA_K2_V7 for long units in many waves
+ *                        up to 64 key steps and for longer units whenever its balanced tail is planned,
+ *                        CA_K2_V7 for long units in well-filled waves
  *            CA_K2_V3    round-1 kernel: P overlays S in TMEM, two softmax warpgroups share a
  *                        tile; the only one with the stream-K tail (uses `workspace`)
  *            CA_K2_V7    P through shared memory, a tile's score buffer is free once loaded
  *            CA_K2_V11   one score buffer shared by the two tiles, P in TMEM, five K/V stages
  *            CA_K2_V11P  the same kernel persistent: one CTA per SM walks the unit list, the mbarrier
- *                        phases run on from unit to unit (no TMEM / barrier set-up or CTA launch per unit)
+ *                        phases run on from unit to unit (no TMEM / barrier set-up or CTA launch per unit);
+ *                        with `workspace`: whole waves of units in lockstep, then the left-over units
+ *                        cut into equal key-step ranges per CTA (fp32 merge in fixed order)
  *   plan_sms 0 = plan the stream-K tail for the real SM count with the measured thresholds,
- *            < 0 = never split, n > 0 = plan for n SMs (parity tests of the tail on any GPU)
+ *            < 0 = never split, n > 0 = plan for n SMs (parity tests of the tail on any GPU).
+ *            CA_K2_V11P balances with key-step ranges over its persistent CTAs instead (same
+ *            workspace mechanism): 0 = when the measured rule says they pay, < 0 = never,
+ *            > 0 = whenever structurally possible (tests and A/B runs)
  * All kernels compute the same function to bf16 round-off; CA_ERR_INVALID_ARG for an unknown impl. */
 enum { CA_K2_AUTO = 0, CA_K2_V3 = 1, CA_K2_V7 = 2, CA_K2_V11 = 3, CA_K2_V11P = 4 };
 size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,

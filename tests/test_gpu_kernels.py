@@ -228,11 +228,13 @@ def test_joint_attention_every_kernel_matches_oracle(ops, impl, B, H, P, T, C, m
 
 
 @pytest.mark.parametrize("B,H,P,T,C,mode", [(1, 8, 2048, 128, 3, 0), (1, 6, 4096, 512, 20, 0), (2, 12, 1300, 200, 5, 1),
-                                            (1, 3, 16384, 256, 32, 0)])
+                                            (1, 3, 16384, 256, 32, 0), (1, 24, 4096, 256, 4, 0)])
 def test_joint_attention_persistent_key_step_ranges(ops, B, H, P, T, C, mode):
-    """CA_K2_V11P with stream-K on (the default for these shapes): every CTA works on an equal share
-    of the key steps, units cut by a share boundary are merged in fp32 by the piece that finishes
-    last.  Must match the one-unit-per-CTA kernel to a bf16 ulp (fp32 merge vs in-TMEM accumulation),
+    """CA_K2_V11P with its balanced tail (plan_sms = 1: whenever structurally possible; the default
+    plans it when the measured rule says it pays): whole waves of units in lockstep, then every CTA
+    works on an equal share of the key steps of the left-over units — all units when there is less
+    than one wave, 136 of 408 at the last shape — and units cut by a share boundary are merged in
+    fp32 by the piece that finishes last.  Must match the one-unit-per-CTA kernel to a bf16 ulp (fp32 merge vs in-TMEM accumulation),
     the oracle like every kernel, and be REPRODUCIBLE bit for bit (fixed merge order); plan_sms < 0
     turns the ranges off (whole units, no workspace)."""
     from conceptattention_b200 import _cabi
@@ -240,11 +242,11 @@ def test_joint_attention_persistent_key_step_ranges(ops, B, H, P, T, C, mode):
     N = P + T + C
     q, k, v = (rnd(B, H, N, 128, seed=s_, scale=sc).cuda() for s_, sc in ((60, 1.5), (61, 1.0), (62, 1.0)))
     V11P, V11 = _cabi.K2_V11P, _cabi.K2_V11
-    assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, V11P, 0) > 0, "ranges not planned: pick other sizes"
+    assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, V11P, 1) > 0, "ranges not planned: pick other sizes"
     assert lib.ca_joint_attention_workspace_bytes_ex(B, H, P, T, C, mode, V11P, -1) == 0
     base = ops.joint_attention(q, k, v, P, T, C, mode, impl=V11)
     whole = ops.joint_attention(q, k, v, P, T, C, mode, impl=V11P, plan_sms=-1)
-    runs = [ops.joint_attention(q, k, v, P, T, C, mode, impl=V11P) for _ in range(3)]
+    runs = [ops.joint_attention(q, k, v, P, T, C, mode, impl=V11P, plan_sms=1) for _ in range(3)]
     auto = ops.joint_attention(q, k, v, P, T, C, mode)
     torch.cuda.synchronize()
     for got, b, w in zip(runs[0], base, whole):
