@@ -752,16 +752,24 @@ static size_t skp_workspace_bytes(const SkpPlan& pl) {
 }
 }  // namespace ca
 
-// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO, measured on B200 (148 SMs;
-// alternating single-shape runs of 60 launches, profiles/r02_k2_variants.md): the persistent v11 up to
-// 64 key steps per query-tile unit (config 2 +2 %, config 3 +8 %, config 4 +6 % over one unit per CTA)
-// and for longer units whenever its balanced tail is planned (config 5: 24 heads 2.64 vs 2.70 ms for
-// v7, 12 heads 1.26 vs 1.36, 3 heads 0.32 vs 0.45); v7 for long units in well-filled waves.
+// Which kernel a launch uses (include/conceptattention_b200.h).  CA_K2_AUTO follows what was measured
+// INSIDE the pipeline (bench.py with CA_K2_IMPL=..., profiles/r02_k2_variants.md), which differs from the
+// isolated launches of scripts/bench_attention.py: in isolation the persistent v11 is 1-8 % ahead of one
+// unit per CTA on every shape, inside a forward (other kernels before and after, SM clock ~1.45 GHz under
+// the power cap) it is 2-8 % behind at configs 2-4 and at config 5 on one GPU (0.245 vs 0.225 ms, 2.95
+// vs 2.88 ms) — its static unit-to-CTA assignment cannot absorb SMs that start late or run slower, the
+// hardware scheduler of the one-unit-per-CTA launch can.  It stays ahead where its balanced tail removes
+// a mostly empty last wave: config 5 sharded over 8 GPUs (3 heads: 0.371 vs 0.408-0.437 ms in the 8-GPU
+// run) and over 2 (12 heads, isolated 1.26 vs 1.36-1.45).
 static int resolve_impl(int impl, int B, int H, int P, int T, int C, int mode) {
   if (impl != CA_K2_AUTO) return impl;
   const int n_steps = (P + T + ca::kBM - 1) / ca::kBM;
-  if (n_steps <= 64) return CA_K2_V11P;
-  return ca::plan_v11p(B, H, P, T, C, mode).on ? CA_K2_V11P : CA_K2_V7;
+  if (n_steps > 64) {
+    const ca::SkpPlan sp = ca::plan_v11p(B, H, P, T, C, mode);
+    const int64_t entries = sp.n_dp + sp.R + ((C > 0 && mode != CA_ATTN_NEITHER) ? (int64_t)B * H : 0);
+    if (sp.on && entries < (int64_t)8 * sp.G) return CA_K2_V11P;
+  }
+  return CA_K2_V11;
 }
 
 extern "C" size_t ca_joint_attention_workspace_bytes_ex(int B, int H, int P, int T, int C, int mode,

@@ -5,6 +5,8 @@ from __future__ import annotations
 
 import math
 
+import os
+
 import torch
 
 from . import _cabi
@@ -247,8 +249,13 @@ def seq_unpack_out(recv, Pl, Tl, C, out=None):
     return attn_img, attn_tc
 
 
+# A/B runs of whole pipelines (bench.py): CA_K2_IMPL=<CA_K2_* id> makes every call that does not name
+# a kernel use that one.  Read once at import, passed per call; the library itself has no switches.
+_DEFAULT_K2_IMPL = int(os.environ.get("CA_K2_IMPL", str(_cabi.K2_AUTO)))
+
+
 def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_txtc=None,
-                    impl=_cabi.K2_AUTO, plan_sms=0):
+                    impl=None, plan_sms=0):
     """One-way joint attention over [img|txt|concept]; returns (out_img [B,P,H*128],
     out_txtc [B,T+C,H*128]).  impl / plan_sms: the per-call kernel and stream-K plan arguments of
     ca_joint_attention_ex (K2_AUTO / 0 = what the product uses)."""
@@ -256,6 +263,8 @@ def joint_attention(q, k, v, P, T, C, mode=_cabi.ATTN_BOTH, out_img=None, out_tx
         _req(t, BF16, n)
     B, H, N, d = q.shape
     assert d == 128 and N == P + T + C and k.shape == q.shape and v.shape == q.shape
+    if impl is None:
+        impl = _DEFAULT_K2_IMPL
     if out_img is None:
         out_img = torch.empty(B, P, H * 128, device=q.device, dtype=BF16)
     if out_txtc is None:

@@ -134,9 +134,9 @@ ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v,
                                 void* workspace, size_t workspace_bytes, void* stream);
 
 /* Same, with the kernel and the tail plan chosen PER CALL (no process-wide switches):
- *   impl     CA_K2_AUTO  the default of the two calls above (measured on B200): CA_K2_V11P for units of
- *                        up to 64 key steps and for longer units whenever its balanced tail is planned,
- *                        CA_K2_V7 for long units in well-filled waves
+ *   impl     CA_K2_AUTO  the default of the two calls above (measured inside the pipeline on B200):
+ *                        CA_K2_V11, except long units (> 64 key steps) in fewer than eight waves whose
+ *                        left-over wave is worth balancing: CA_K2_V11P with its key-step ranges
  *            CA_K2_V3    round-1 kernel: P overlays S in TMEM, two softmax warpgroups share a
  *                        tile; the only one with the stream-K tail (uses `workspace`)
  *            CA_K2_V7    P through shared memory, a tile's score buffer is free once loaded
