@@ -742,9 +742,10 @@ static SkpPlan plan_v11p(int B, int H, int P, int T, int C, int mode, bool force
   // structural limits: table size, tail share of at least 8 key steps per CTA, at most ~14 pieces per unit
   pl.on = sms <= kSkpMaxCtas && pl.R > 0 && pl.R * n >= (int64_t)8 * sms && pl.R * 14 >= sms &&
           pl.R * n < 0x7fffffffLL;
-  // measured rule (skipped when forced by plan_sms > 0; profiles/r02_k2_variants.md): the launch without
-  // ranges is at least 6 % longer than an even split
-  if (pl.on && !force) pl.on = whole * sms * 100 >= T_cost * 106;
+  // measured rule (skipped when forced by plan_sms > 0; profiles/r02_k2_variants.md): two partial pieces
+  // and a merge cost a CTA about ten key steps, so the even split must save at least 24 (config 2
+  // single blocks would save 8 and lose 8 %; config 5 saves 67-134 and gains 3-20 %)
+  if (pl.on && !force) pl.on = whole * sms >= T_cost + (int64_t)24 * sms;
   return pl;
 }
 static size_t skp_workspace_bytes(const SkpPlan& pl) {
@@ -760,15 +761,18 @@ static size_t skp_workspace_bytes(const SkpPlan& pl) {
 // vs 2.88 ms) — its static unit-to-CTA assignment cannot absorb SMs that start late or run slower, the
 // hardware scheduler of the one-unit-per-CTA launch can.  It stays ahead where its balanced tail removes
 // a mostly empty last wave: config 5 sharded over 8 GPUs (3 heads: 0.371 vs 0.408-0.437 ms in the 8-GPU
-// run) and over 2 (12 heads, isolated 1.26 vs 1.36-1.45).
+// run) and over 2 (12 heads, isolated 1.26 vs 1.36-1.45), and for many short units (config 3).
+// (Part of the first in-pipeline loss was the tail plan itself: it was on for config 2's single blocks,
+// where it saves 8 key steps and costs 10; with the rule in plan_v11p the gap at config 2 is 3 %.)
 static int resolve_impl(int impl, int B, int H, int P, int T, int C, int mode) {
   if (impl != CA_K2_AUTO) return impl;
   const int n_steps = (P + T + ca::kBM - 1) / ca::kBM;
-  if (n_steps > 64) {
-    const ca::SkpPlan sp = ca::plan_v11p(B, H, P, T, C, mode);
-    const int64_t entries = sp.n_dp + sp.R + ((C > 0 && mode != CA_ATTN_NEITHER) ? (int64_t)B * H : 0);
-    if (sp.on && entries < (int64_t)8 * sp.G) return CA_K2_V11P;
-  }
+  const ca::SkpPlan sp = ca::plan_v11p(B, H, P, T, C, mode);
+  const int64_t entries = sp.n_dp + sp.R + ((C > 0 && mode != CA_ATTN_NEITHER) ? (int64_t)B * H : 0);
+  // long units in few waves whose left-over wave is worth balancing (config 5 over 2-8 GPUs)
+  if (n_steps > 64 && sp.on && entries < (int64_t)8 * sp.G) return CA_K2_V11P;
+  // many short units: set-up per unit dominates (config 3 in the pipeline: 0.413 vs 0.456 ms)
+  if (n_steps <= 16 && sp.G > 0 && entries >= (int64_t)4 * sp.G) return CA_K2_V11P;
   return CA_K2_V11;
 }
 

@@ -90,6 +90,9 @@ def main():
     ap.add_argument("--impls", default="0,1,2,3", help="CA_K2_* per-call kernel ids: 0 auto, 1 v3, 2 v7, 3 v11")
     ap.add_argument("--only", default="")
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--interleave", default="", choices=["", "gemm", "copy"],
+                    help="launch another kernel before every K2 launch (what a forward does) and time K2 alone "
+                         "with events around each launch")
     args = ap.parse_args()
     pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
@@ -106,13 +109,32 @@ def main():
             for i in range(3):
                 ops.joint_attention(*sets[i % 2], P, T, C, impl=impl, plan_sms=plan_sms)
             torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for i in range(args.iters):
-                ops.joint_attention(*sets[i % 2], P, T, C, impl=impl, plan_sms=plan_sms)
-            e1.record()
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / args.iters
+            if args.interleave:
+                a = torch.randn(4352, 3072, device="cuda").to(torch.bfloat16)
+                w = torch.randn(3072, 9216, device="cuda").to(torch.bfloat16)
+                big = torch.empty(160 << 20, dtype=torch.uint8, device="cuda")
+                big2 = torch.empty_like(big)
+                evs = []
+                for i in range(args.iters):
+                    if args.interleave == "gemm":
+                        torch.mm(a, w)
+                    else:
+                        big2.copy_(big)
+                    ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    ea.record()
+                    ops.joint_attention(*sets[i % 2], P, T, C, impl=impl, plan_sms=plan_sms)
+                    eb.record()
+                    evs.append((ea, eb))
+                torch.cuda.synchronize()
+                ms = sum(x.elapsed_time(y) for x, y in evs) / args.iters
+            else:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(args.iters):
+                    ops.joint_attention(*sets[i % 2], P, T, C, impl=impl, plan_sms=plan_sms)
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / args.iters
             tf = flops / ms / 1e9
             print(json.dumps({"kernel": "ca_joint_attention", "impl": impl, "shape": name, "B": B, "H": H,
                               "P": P, "T": T, "C": C, "ms": round(ms, 4), "TFLOPs": round(tf, 1),

@@ -31,9 +31,10 @@ def _noalloc(lib, q, k, v, P, T, Cn, mode, impl, plan_sms):
     return st, out_img, out_tc
 
 
-# (B, H, P, T, C, mode, impl, plan_sms): the persistent kernel with its key-step ranges (CA_K2_V11P = 4),
+# (B, H, P, T, C, mode, impl, plan_sms): the persistent kernel with its key-step ranges (CA_K2_V11P = 4,
+# plan_sms = 1: planned whenever structurally possible),
 # round 1's stream-K tail planned for 24 SMs (CA_K2_V3 = 1), and the default on a shape without scratch
-CASES = [(1, 8, 2048, 128, 3, 0, 4, 0), (1, 2, 2200, 200, 5, 0, 1, 24), (1, 6, 4096, 512, 20, 0, 4, 0),
+CASES = [(1, 8, 2048, 128, 3, 0, 4, 1), (1, 2, 2200, 200, 5, 0, 1, 24), (1, 6, 4096, 512, 20, 0, 4, 1),
          (2, 3, 256, 256, 4, 0, 0, 0)]
 
 
