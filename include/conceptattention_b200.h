@@ -135,8 +135,9 @@ ca_status ca_joint_attention_ws(const void* q, const void* k, const void* v,
 
 /* Same, with the kernel and the tail plan chosen PER CALL (no process-wide switches):
  *   impl     CA_K2_AUTO  the default of the two calls above (measured inside the pipeline on B200):
- *                        CA_K2_V11, except long units (> 64 key steps) in fewer than eight waves whose
- *                        left-over wave is worth balancing: CA_K2_V11P with its key-step ranges
+ *                        CA_K2_V11, except CA_K2_V11P for many short units (<= 16 key steps in >= 4
+ *                        waves of the SMs) and for long units (> 64 key steps) in fewer than eight
+ *                        waves whose left-over wave is worth balancing with its key-step ranges
  *            CA_K2_V3    round-1 kernel: P overlays S in TMEM, two softmax warpgroups share a
  *                        tile; the only one with the stream-K tail (uses `workspace`)
  *            CA_K2_V7    P through shared memory, a tile's score buffer is free once loaded
